@@ -1,0 +1,377 @@
+// heat_b200/csrc/heat_abi.cu -- the extern "C" surface of include/heat_b200.h.
+#include <cstring>
+#include <new>
+#include "heat_ctx.cuh"
+#include "index_kernels.cuh"
+
+namespace heat {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string &msg) { g_last_error = msg; }
+int fail(const std::string &msg) { g_last_error = msg; return 1; }
+
+namespace {
+
+// uint64 host layout -> int32 device layout; flags ids that do not fit their table.
+__global__ void narrow_ids_kernel(const unsigned long long *src, int *dst, size_t n, unsigned long long limit_even,
+                                  unsigned long long limit_odd, int *bad)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const unsigned long long v = src[i];
+        const unsigned long long lim = (i & 1) ? limit_odd : limit_even;
+        if (v >= lim) atomicExch(bad, 1);
+        dst[i] = (int)v;
+    }
+}
+
+int upload_narrow(Ctx *c, const uint64_t *host, size_t n, int *dst, uint64_t lim_even, uint64_t lim_odd, const char *what)
+{
+    unsigned long long *stage = nullptr;
+    int *bad = nullptr;
+    HEAT_CUDA(cudaMalloc(&stage, n * sizeof(uint64_t)));
+    HEAT_CUDA(cudaMalloc(&bad, sizeof(int)));
+    HEAT_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(stage, host, n * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    const int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)c->num_sms * 8);
+    narrow_ids_kernel<<<blocks > 0 ? blocks : 1, 256, 0, c->stream>>>(stage, dst, n, lim_even, lim_odd, bad);
+    c->launches += 1;
+    int h_bad = 0;
+    HEAT_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(stage); cudaFree(bad);
+    if (h_bad) return fail(std::string(what) + ": id out of range for its table");
+    return 0;
+}
+
+void free_dataset(Ctx *c)
+{
+    cudaFree(c->clicks); cudaFree(c->his); cudaFree(c->masks);
+    c->clicks = nullptr; c->his = nullptr; c->masks = nullptr;
+}
+void free_tables(Ctx *c)
+{
+    cudaFree(c->user_w); cudaFree(c->item_w); cudaFree(c->user_g); cudaFree(c->item_g); cudaFree(c->w0);
+    cudaFree(c->item_base); cudaFree(c->w0_base);
+    c->user_w = c->item_w = c->user_g = c->item_g = c->w0 = c->item_base = c->w0_base = nullptr;
+}
+
+TrainParams index_params(Ctx *c, uint64_t epoch, uint64_t begin, uint64_t end)
+{
+    TrainParams P{};
+    P.clicks = c->clicks; P.his = c->his; P.masks = c->masks;
+    P.begin = (long long)begin; P.end = (long long)end;
+    P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed; P.epoch = (unsigned)epoch;
+    P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
+    return P;
+}
+
+}  // namespace
+}  // namespace heat
+
+using namespace heat;
+
+extern "C" {
+
+int heat_abi_version(void) { return HEAT_ABI_VERSION; }
+const char *heat_last_error(void) { return g_last_error.c_str(); }
+
+int heat_create(heat_ctx **out, const heat_config *cfg, int device)
+{
+    if (!out || !cfg) return fail("heat_create: null argument");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(std::string("heat_create: no CUDA device (") + cudaGetErrorString(e) +
+                    "); this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail("heat_create: device index out of range");
+    HEAT_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop{};
+    HEAT_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(std::string("heat_create: built for sm_100a, found ") + prop.name);
+    if (cfg->emb_dim == 0 || cfg->num_negs == 0 || cfg->num_items == 0 || cfg->num_users == 0)
+        return fail("heat_create: emb_dim, num_negs, num_users and num_items must be non-zero");
+    if (cfg->num_items >= (1ull << 31) || cfg->num_users >= (1ull << 31))
+        return fail("heat_create: ids must fit int32");
+
+    Ctx *c = new (std::nothrow) Ctx();
+    if (!c) return fail("heat_create: out of host memory");
+    c->cfg = *cfg;
+    c->milestones.assign(cfg->milestones, cfg->milestones + (cfg->milestones ? cfg->n_milestones : 0));
+    c->cfg.milestones = nullptr;
+    if (c->cfg.seed == 0) c->cfg.seed = 2022;
+    if (c->cfg.chunk == 0) c->cfg.chunk = 64;
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    c->l_r = cfg->l_r;
+    HEAT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    HEAT_CUDA(cudaEventCreate(&c->ev0));
+    HEAT_CUDA(cudaEventCreate(&c->ev1));
+    HEAT_CUDA(cudaMalloc(&c->chunk_counter, sizeof(unsigned long long)));
+    HEAT_CUDA(cudaMalloc(&c->loss_sum, sizeof(double)));
+    *out = reinterpret_cast<heat_ctx *>(c);
+    return 0;
+}
+
+int heat_destroy(heat_ctx *ctx)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    comm_destroy(c);
+    free_dataset(c); free_tables(c);
+    cudaFree(c->chunk_counter); cudaFree(c->loss_sum); cudaFree(c->eval_scratch);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return 0;
+}
+
+int heat_set_dataset(heat_ctx *ctx, const uint64_t *clicks, uint64_t n, const uint64_t *his_items,
+                     uint64_t num_users, uint64_t max_his, const uint64_t *masks)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !clicks || !his_items || !masks) return fail("heat_set_dataset: null argument");
+    if (num_users != c->cfg.num_users) return fail("heat_set_dataset: num_users differs from the config");
+    if (n >= (1ull << 40)) return fail("heat_set_dataset: too many samples");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    free_dataset(c);
+    c->n_samples = n; c->max_his = max_his; c->cfg.train_size = n;
+    HEAT_CUDA(cudaMalloc(&c->clicks, (n ? n : 1) * sizeof(int2)));
+    HEAT_CUDA(cudaMalloc(&c->his, (num_users * max_his ? num_users * max_his : 1) * sizeof(int)));
+    HEAT_CUDA(cudaMalloc(&c->masks, num_users * sizeof(int)));
+    int rc = 0;
+    if (n) rc = upload_narrow(c, clicks, 2 * n, reinterpret_cast<int *>(c->clicks), c->cfg.num_users, c->cfg.num_items, "clicks");
+    if (!rc && num_users * max_his)
+        rc = upload_narrow(c, his_items, num_users * max_his, c->his, c->cfg.num_items, c->cfg.num_items, "historical_items");
+    if (!rc) rc = upload_narrow(c, masks, num_users, c->masks, max_his + 1, max_his + 1, "masks");
+    return rc;
+}
+
+int heat_bind_tables(heat_ctx *ctx, float *user_w, float *item_w, float *w0)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !user_w || !item_w || !w0) return fail("heat_bind_tables: null argument");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    free_tables(c);
+    const size_t D = c->cfg.emb_dim, ub = c->cfg.num_users * D * sizeof(float), ib = c->cfg.num_items * D * sizeof(float);
+    HEAT_CUDA(cudaMalloc(&c->user_w, ub)); HEAT_CUDA(cudaMalloc(&c->user_g, ub));
+    HEAT_CUDA(cudaMalloc(&c->item_w, ib)); HEAT_CUDA(cudaMalloc(&c->item_g, ib));
+    HEAT_CUDA(cudaMalloc(&c->w0, D * D * sizeof(float)));
+    c->h_user_w = user_w; c->h_item_w = item_w; c->h_w0 = w0;
+    int rc = heat_upload_tables(ctx);
+    if (!rc) rc = heat_zero_grad(ctx);
+    return rc;
+}
+
+int heat_upload_tables(heat_ctx *ctx)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !c->user_w) return fail("heat_upload_tables: no tables bound");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t D = c->cfg.emb_dim;
+    HEAT_CUDA(cudaMemcpyAsync(c->user_w, c->h_user_w, c->cfg.num_users * D * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(c->item_w, c->h_item_w, c->cfg.num_items * D * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(c->w0, c->h_w0, D * D * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    if (c->item_base) {
+        HEAT_CUDA(cudaMemcpyAsync(c->item_base, c->item_w, c->cfg.num_items * D * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+        HEAT_CUDA(cudaMemcpyAsync(c->w0_base, c->w0, D * D * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+    }
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int heat_sync_to_host(heat_ctx *ctx)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !c->user_w) return fail("heat_sync_to_host: no tables bound");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t D = c->cfg.emb_dim;
+    HEAT_CUDA(cudaMemcpyAsync(c->h_user_w, c->user_w, c->cfg.num_users * D * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(c->h_item_w, c->item_w, c->cfg.num_items * D * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(c->h_w0, c->w0, D * D * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int heat_zero_grad(heat_ctx *ctx)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !c->user_g) return fail("heat_zero_grad: no tables bound");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t D = c->cfg.emb_dim;
+    HEAT_CUDA(cudaMemsetAsync(c->user_g, 0, c->cfg.num_users * D * sizeof(float), c->stream));
+    HEAT_CUDA(cudaMemsetAsync(c->item_g, 0, c->cfg.num_items * D * sizeof(float), c->stream));
+    return 0;
+}
+
+int heat_train_range(heat_ctx *ctx, uint64_t begin, uint64_t end, double *loss_sum, float *loss_per_sample)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_train_range: null context");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return launch_train(c, begin, end, loss_sum, loss_per_sample);
+}
+
+int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_train_epoch: null context");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    // LR schedule, engine.cpp:156-160 -> optimizer.cpp:24-38 (decay 0.1)
+    if (c->milestones.size() > 1) {
+        for (uint64_t m : c->milestones)
+            if (m == c->epoch) { c->l_r = c->l_r * 0.1f; break; }
+    } else if (c->milestones.size() == 1 && c->milestones[0] != 0) {
+        if (c->epoch > 0 && c->epoch % c->milestones[0] == 0) c->l_r = c->l_r * 0.1f;
+    }
+    const uint64_t N = c->n_samples;
+    double total = 0.0;
+    float ms_total = 0.f;
+    const uint64_t step = (c->world > 1 && c->sync_interval) ? c->sync_interval : N;
+    for (uint64_t b = 0; b < N; b += step) {
+        const uint64_t e = std::min(N, b + step);
+        double part = 0.0;
+        int rc = launch_train(c, b, e, &part, nullptr);
+        if (rc) return rc;
+        total += part; ms_total += c->last_kernel_ms;
+        if (c->world > 1) { rc = comm_sync_items(c); if (rc) return rc; }
+    }
+    c->last_kernel_ms = ms_total;
+    int rc = heat_zero_grad(ctx);                       // engine.cpp:345-347
+    if (rc) return rc;
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    c->epoch += 1;                                      // engine.cpp:378
+    if (mean_loss) *mean_loss = N ? total / (double)N : 0.0;
+    return 0;
+}
+
+int heat_get_grads(heat_ctx *ctx, float *user_g, float *item_g)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !c->user_g) return fail("heat_get_grads: no tables bound");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t D = c->cfg.emb_dim;
+    if (user_g) HEAT_CUDA(cudaMemcpyAsync(user_g, c->user_g, c->cfg.num_users * D * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (item_g) HEAT_CUDA(cudaMemcpyAsync(item_g, c->item_g, c->cfg.num_items * D * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int heat_set_lr(heat_ctx *ctx, float l_r) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c) return fail("null context"); c->l_r = l_r; return 0; }
+int heat_get_lr(heat_ctx *ctx, float *l_r) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !l_r) return fail("null argument"); *l_r = c->l_r; return 0; }
+int heat_get_epoch(heat_ctx *ctx, uint64_t *epoch) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !epoch) return fail("null argument"); *epoch = c->epoch; return 0; }
+int heat_set_epoch(heat_ctx *ctx, uint64_t epoch) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c) return fail("null context"); c->epoch = epoch; return 0; }
+int heat_last_kernel_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_kernel_ms; return 0; }
+int heat_last_eval_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_eval_ms; return 0; }
+int heat_launch_count(heat_ctx *ctx, uint64_t *n) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !n) return fail("null argument"); *n = c->launches; return 0; }
+
+int heat_sample_negatives(heat_ctx *ctx, uint64_t epoch, uint64_t begin, uint64_t end, uint64_t *out)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !out) return fail("heat_sample_negatives: null argument");
+    if (!c->clicks) return fail("heat_sample_negatives: heat_set_dataset has not been called");
+    if (end > c->n_samples || begin > end) return fail("heat_sample_negatives: range out of bounds");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t n = (end - begin) * c->cfg.num_negs;
+    if (!n) return 0;
+    unsigned long long *d = nullptr;
+    HEAT_CUDA(cudaMalloc(&d, n * sizeof(uint64_t)));
+    const TrainParams P = index_params(c, epoch, begin, end);
+    sample_negatives_kernel<<<c->num_sms * 4, 256, 0, c->stream>>>(P, d);
+    c->launches += 1;
+    HEAT_CUDA(cudaGetLastError());
+    HEAT_CUDA(cudaMemcpyAsync(out, d, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d);
+    return 0;
+}
+
+int heat_history_indices(heat_ctx *ctx, uint64_t begin, uint64_t end, uint64_t *out_ids, uint64_t *out_count)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !out_ids || !out_count) return fail("heat_history_indices: null argument");
+    if (!c->clicks) return fail("heat_history_indices: heat_set_dataset has not been called");
+    if (end > c->n_samples || begin > end) return fail("heat_history_indices: range out of bounds");
+    if (c->max_his > 128) return fail("max_his > 128 is not supported");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t n = end - begin;
+    if (!n) return 0;
+    unsigned long long *d_ids = nullptr, *d_cnt = nullptr;
+    HEAT_CUDA(cudaMalloc(&d_ids, n * c->max_his * sizeof(uint64_t)));
+    HEAT_CUDA(cudaMalloc(&d_cnt, n * sizeof(uint64_t)));
+    const TrainParams P = index_params(c, 0, begin, end);
+    history_indices_kernel<<<c->num_sms * 4, 256, 0, c->stream>>>(P, d_ids, d_cnt);
+    c->launches += 1;
+    HEAT_CUDA(cudaGetLastError());
+    HEAT_CUDA(cudaMemcpyAsync(out_ids, d_ids, n * c->max_his * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(out_count, d_cnt, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d_ids); cudaFree(d_cnt);
+    return 0;
+}
+
+uint64_t heat_philox_draw(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k, uint64_t num_items)
+{
+    return philox_draw(seed, (uint32_t)epoch, sample, k, (uint32_t)num_items);
+}
+
+int heat_eval_dense(heat_ctx *ctx, float *out)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !out) return fail("heat_eval_dense: null argument");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return eval_dense(c, out);
+}
+int heat_eval_topk(heat_ctx *ctx, uint32_t k, const int64_t *train_indptr, const int32_t *train_items,
+                   int32_t *topk_ids, float *topk_scores)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !topk_ids) return fail("heat_eval_topk: null argument");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return eval_topk(c, k, train_indptr, train_items, topk_ids, topk_scores);
+}
+int heat_eval_metrics(heat_ctx *ctx, const int64_t *train_indptr, const int32_t *train_items,
+                      const int64_t *test_indptr, const int32_t *test_items, double out[6], double sums_out[7])
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !test_indptr || !test_items || !out) return fail("heat_eval_metrics: null argument");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return eval_metrics(c, train_indptr, train_items, test_indptr, test_items, out, sums_out);
+}
+
+int heat_comm_unique_id(uint8_t out[128]) { return comm_unique_id(out); }
+int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[128])
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_comm_init: null context");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return comm_init(c, rank, world, unique_id);
+}
+int heat_comm_sync_items(heat_ctx *ctx)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_comm_sync_items: null context");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return comm_sync_items(c);
+}
+int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_set_sync_interval: null context");
+    c->sync_interval = samples;
+    return 0;
+}
+
+int heat_probe_l2_bandwidth(int device, uint64_t bytes, int iters, double *gbps) { return probe_l2(device, bytes, iters, gbps); }
+
+int heat_host_alloc(void **ptr, uint64_t bytes)
+{
+    if (!ptr) return fail("heat_host_alloc: null argument");
+    HEAT_CUDA(cudaHostAlloc(ptr, bytes, cudaHostAllocDefault));
+    return 0;
+}
+int heat_host_free(void *ptr) { HEAT_CUDA(cudaFreeHost(ptr)); return 0; }
+
+}  // extern "C"

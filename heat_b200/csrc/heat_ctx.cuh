@@ -1,0 +1,74 @@
+// heat_b200/csrc/heat_ctx.cuh -- device-resident state behind the C ABI (include/heat_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/heat_b200.h"
+
+namespace heat {
+
+// HBM layout (all allocations 256-byte aligned by cudaMalloc):
+//   clicks  int2 [N]            8 B/sample          his    int32 [U, max_his]
+//   masks   int32 [U]                               user_w fp32 [U, D]   user_g fp32 [U, D]
+//   item_w  fp32 [I, D]   item_g fp32 [I, D]        w0     fp32 [D, D]
+//   item_base / w0_base (multi-GPU only): copies taken at the last sync, for the delta all-reduce
+struct Ctx {
+    heat_config cfg{};
+    std::vector<uint64_t> milestones;
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    int2 *clicks = nullptr;
+    int *his = nullptr, *masks = nullptr;
+    uint64_t n_samples = 0, max_his = 0;
+    float *user_w = nullptr, *item_w = nullptr, *user_g = nullptr, *item_g = nullptr, *w0 = nullptr;
+    float *h_user_w = nullptr, *h_item_w = nullptr, *h_w0 = nullptr;   // bound host buffers
+    unsigned long long *chunk_counter = nullptr;
+    double *loss_sum = nullptr;
+
+    float l_r = 0.f;          // optimizer LR (scheduled); cfg.l_r stays the aggregator's LR
+    uint64_t epoch = 0;
+    float last_kernel_ms = 0.f, last_eval_ms = 0.f;
+    uint64_t launches = 0;
+
+    // multi-GPU
+    int rank = 0, world = 1;
+    void *nccl_comm = nullptr;
+    float *item_base = nullptr, *w0_base = nullptr;
+    uint64_t sync_interval = 0;
+
+    // evaluation scratch (lazily sized)
+    void *eval_scratch = nullptr;
+    size_t eval_scratch_bytes = 0;
+};
+
+void set_error(const std::string &msg);
+int fail(const std::string &msg);
+
+#define HEAT_CUDA(expr)                                                                          \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess)                                                                   \
+            return ::heat::fail(std::string(#expr) + ": " + cudaGetErrorString(_e));             \
+    } while (0)
+
+// train_launch.cu
+int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host);
+// eval_kernel.cu
+int eval_dense(Ctx *c, float *out_host);
+int eval_topk(Ctx *c, uint32_t k, const int64_t *train_indptr, const int32_t *train_items,
+              int32_t *topk_ids_host, float *topk_scores_host);
+int eval_metrics(Ctx *c, const int64_t *train_indptr, const int32_t *train_items,
+                 const int64_t *test_indptr, const int32_t *test_items, double out[6], double sums[7]);
+// comm.cu
+int comm_unique_id(uint8_t out[128]);
+int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128]);
+int comm_sync_items(Ctx *c);
+void comm_destroy(Ctx *c);
+// probe.cu
+int probe_l2(int device, uint64_t bytes, int iters, double *gbps);
+
+}  // namespace heat

@@ -1,0 +1,379 @@
+// heat_b200/csrc/train_kernel.cuh -- fused forward + backward + clipped-SGD kernel, sm_100a.
+//
+// One WARP owns one sample at a time; a warp takes `chunk` consecutive samples per
+// scheduling step from a global counter (the GPU form of the reference's
+// `#pragma omp for schedule(dynamic,512)`, train/engine.cpp:327) and walks them in file
+// order, so a user's consecutive samples are applied sequentially exactly as one OpenMP
+// thread would apply them.  Different warps race on shared rows Hogwild-style, as the
+// reference's threads do (ICS23-HEAT.pdf section 4.5).
+//
+// What one sample does (reference: models/matrix_factorization.cpp:15-181,
+// behavior_aggregators/behavior_aggregators.cpp:51-153, optimizers/sgd.cpp:14-26):
+//   gather U[u], I[p], the K negative rows, their persistent grad rows and the H history
+//   rows (float4 per lane, D/4 lanes per row, 32/(D/4) rows per warp-wide load, L2-coherent
+//   ld.global.cg); mean -> mean.W0 (W0 staged in shared memory) -> u = 0.4u + 0.6f;
+//   warp-shuffle dots, cosine, temperature-0.07 softmax loss with the implicit zero logit;
+//   closed-form cosine grads reusing the forward dots/norms; g = clamp(g_prev + dg);
+//   w -= lr*g; both rows written back; W0 outer-product grads buffered per warp in a
+//   32-slot shared-memory ring and applied every 32 samples (behavior_aggregators.cpp:141-146).
+//
+// Layout: tables are row-major fp32 [rows, D]; ids int32; one row = D*4 bytes = one or two
+// 128-byte lines, so every warp-wide LDG.128 moves whole lines.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "philox.cuh"
+
+namespace heat {
+
+struct TrainParams {
+    const int2 *clicks;      // [N] (user, item)
+    const int *his;          // [U, max_his]
+    const int *masks;        // [U]
+    float *user_w, *item_w;  // [U,D], [I,D]
+    float *user_g, *item_g;  // persistent grad rows, zero at epoch start
+    float *w0;               // [D,D] row-major
+    unsigned long long *chunk_counter;
+    double *loss_sum;
+    float *loss_out;         // optional [end-begin]
+    long long begin, end;    // local sample range
+    unsigned long long sample_offset, seed;
+    unsigned epoch;
+    int max_his, num_items, K, chunk, drop_w0_tail;
+    float lr, lr_w0, clip;
+};
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ float4 ldcg4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ void stcg4(float *p, const float4 &v) { __stcg(reinterpret_cast<float4 *>(p), v); }
+__device__ __forceinline__ float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ float4 operator+(const float4 &a, const float4 &b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float4 operator-(const float4 &a, const float4 &b) { return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+__device__ __forceinline__ float4 operator*(float s, const float4 &a) { return make_float4(s * a.x, s * a.y, s * a.z, s * a.w); }
+__device__ __forceinline__ float dot4(const float4 &a, const float4 &b) { return fmaf(a.w, b.w, fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x))); }
+__device__ __forceinline__ void fma4(float4 &acc, float s, const float4 &a)
+{
+    acc.x = fmaf(s, a.x, acc.x); acc.y = fmaf(s, a.y, acc.y); acc.z = fmaf(s, a.z, acc.z); acc.w = fmaf(s, a.w, acc.w);
+}
+__device__ __forceinline__ float clampf(float g, float c) { return fmaxf(fminf(g, c), -c); }   // optimizer.cpp:17-22
+__device__ __forceinline__ float4 clamp4(const float4 &g, float c) { return make_float4(clampf(g.x, c), clampf(g.y, c), clampf(g.z, c), clampf(g.w, c)); }
+
+// sum over the VL lanes that hold one row (result in every lane of the group)
+template <int VL> __device__ __forceinline__ float group_sum(float v)
+{
+#pragma unroll
+    for (int o = VL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+// sum over the 32/VL row groups of the warp
+template <int VL> __device__ __forceinline__ float cross_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o >= VL; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+template <int VL> __device__ __forceinline__ float cross_max(float v)
+{
+#pragma unroll
+    for (int o = 16; o >= VL; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
+    return v;
+}
+template <int VL> __device__ __forceinline__ float4 cross_sum4(float4 v)
+{
+    v.x = cross_sum<VL>(v.x); v.y = cross_sum<VL>(v.y); v.z = cross_sum<VL>(v.z); v.w = cross_sum<VL>(v.w);
+    return v;
+}
+
+// Slot k of local sample s: Philox draw with the reference's "keep the previous value when the
+// draw equals the positive" rule in stateless form (see philox.cuh).
+__device__ __forceinline__ int sample_negative(const TrainParams &P, long long s, int k, int pos)
+{
+    long long t = s;
+    for (;;) {
+        const int d = (int)philox_draw(P.seed, P.epoch, P.sample_offset + (unsigned long long)t, (uint32_t)k,
+                                       (uint32_t)P.num_items);
+        if (d != pos) return d;
+        if (t == 0) return 0;
+        --t;
+        pos = __ldg(&P.clicks[t]).y;
+    }
+}
+
+// History ids of user u: lane holds ids lane, lane+32, lane+64, lane+96 (max_his <= 128).
+__device__ __forceinline__ void load_history_ids(const TrainParams &P, int u, int lane, int (&hid)[4])
+{
+    const int *row = P.his + (size_t)u * P.max_his;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) hid[q] = (lane + 32 * q < P.max_his) ? __ldg(row + lane + 32 * q) : 0;
+}
+__device__ __forceinline__ int pick4(const int (&hid)[4], int q)
+{
+    return q == 0 ? hid[0] : q == 1 ? hid[1] : q == 2 ? hid[2] : hid[3];
+}
+
+// Apply a warp's buffered W0 gradients: W0 -= lr0 * (sum_s mean_s^T (0.6 g_s)) / 32
+// (behavior_aggregators.cpp:131-146).  ring slot s = [mean_s (D) | 0.6*g_s (D)].
+template <int D>
+__device__ __forceinline__ void w0_flush(const float *ring, float *W0s, float *w0g, int cnt, float lr0, int lane)
+{
+    constexpr int CPL = D / 32;   // columns per lane
+    constexpr int IB = 16;        // rows per pass
+    for (int ib = 0; ib < D; ib += IB) {
+        float acc[IB][CPL];
+#pragma unroll
+        for (int i = 0; i < IB; ++i)
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) acc[i][c] = 0.f;
+        for (int s = 0; s < cnt; ++s) {
+            const float *ms = ring + s * 2 * D;
+            float gv[CPL];
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) gv[c] = ms[D + lane * CPL + c];
+#pragma unroll
+            for (int i4 = 0; i4 < IB; i4 += 4) {
+                const float4 m4 = *reinterpret_cast<const float4 *>(ms + ib + i4);
+#pragma unroll
+                for (int c = 0; c < CPL; ++c) {
+                    acc[i4 + 0][c] = fmaf(m4.x, gv[c], acc[i4 + 0][c]);
+                    acc[i4 + 1][c] = fmaf(m4.y, gv[c], acc[i4 + 1][c]);
+                    acc[i4 + 2][c] = fmaf(m4.z, gv[c], acc[i4 + 2][c]);
+                    acc[i4 + 3][c] = fmaf(m4.w, gv[c], acc[i4 + 3][c]);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < IB; ++i)
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) {
+                const int e = (ib + i) * D + lane * CPL + c;
+                const float delta = -(lr0 * (acc[i][c] / 32.0f));
+                const float old = atomicAdd(w0g + e, delta);   // returns the value before: picks up other warps' updates
+                W0s[e] = old + delta;
+            }
+    }
+}
+
+// D: embedding dim (32/64/128).  NJ: negative rows held per row group (K <= NJ * 32/(D/4)).
+// WARPS: warps per block.  PRELOAD_G: negative grad rows loaded up front with the weights.
+template <int D, int NJ, int WARPS, bool PRELOAD_G>
+__global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams P)
+{
+    constexpr int VL = D / 4;        // lanes per row
+    constexpr int R = 32 / VL;       // rows per warp-wide load
+    constexpr int UNR = 8;           // history loads in flight per lane
+    constexpr int IPG = D / R;       // W0 rows per group in the GEMV
+    static_assert(NJ * R <= 32, "negative ids are exchanged by lane index");
+
+    extern __shared__ __align__(16) float smem[];
+    float *W0s = smem;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane / VL, sl = lane % VL;
+    float *ring = smem + D * D + warp * (32 * 2 * D);
+
+    for (int i = threadIdx.x * 4; i < D * D; i += WARPS * 32 * 4)
+        *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
+    __syncthreads();
+
+    const float gamma = 0.4f;                        // behavior_aggregators.cpp:37
+    const float omg = 1.0f - gamma;
+    const float eps = 1e-8f;                         // matrix_factorization.cpp:54
+    const float score_mul = (float)(1.0 / 0.07);     // matrix_factorization.cpp:101
+    const int K = P.K;
+    unsigned iter = 0;                               // BehaviorAggregator::iteration of this warp
+    double loss_acc = 0.0;
+    const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
+
+    for (;;) {
+        unsigned long long c = 0;
+        if (lane == 0) c = atomicAdd(P.chunk_counter, 1ULL);
+        c = __shfl_sync(FULL, c, 0);
+        if ((long long)c >= nchunks) break;
+        const long long s0 = P.begin + (long long)c * P.chunk;
+        const long long s1 = min(P.end, s0 + (long long)P.chunk);
+
+        for (long long s = s0; s < s1; ++s) {
+            __syncwarp();   // rows written by other lanes for the previous sample are visible
+            const int2 up = __ldg(&P.clicks[s]);
+            const int u = up.x, p = up.y;
+
+            // ---- negatives (lane k draws slot k) and duplicate detection
+            int negid = -1 - lane;
+            if (lane < K) negid = sample_negative(P, s, lane, p);
+            const unsigned same = __match_any_sync(FULL, negid);
+            const bool dup = __any_sync(FULL, (same & (same - 1)) != 0);
+
+            // ---- issue the row gathers
+            const float4 uw = ldcg4(P.user_w + (size_t)u * D + 4 * sl);
+            float4 pw = ldcg4(P.item_w + (size_t)p * D + 4 * sl);
+            const float4 gu_old = ldcg4(P.user_g + (size_t)u * D + 4 * sl);
+            const float4 gp_old = ldcg4(P.item_g + (size_t)p * D + 4 * sl);
+            int nid[NJ];
+            float4 nw[NJ];
+            float4 gn[PRELOAD_G ? NJ : 1];
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                const int k = j * R + g;
+                nid[j] = __shfl_sync(FULL, negid, k & 31);
+                const bool ok = k < K;
+                nw[j] = ok ? ldcg4(P.item_w + (size_t)nid[j] * D + 4 * sl) : f4zero();
+                if (PRELOAD_G) gn[j] = ok ? ldcg4(P.item_g + (size_t)nid[j] * D + 4 * sl) : f4zero();
+            }
+
+            // ---- history aggregation (behavior_aggregators.cpp:60-105)
+            const int H = __ldg(P.masks + u);
+            int hid[4];
+            load_history_ids(P, u, lane, hid);
+            float4 acc = f4zero();
+            for (int h0 = 0; h0 < H; h0 += R * UNR) {
+                const int hq = pick4(hid, h0 >> 5);
+                float4 t[UNR];
+#pragma unroll
+                for (int i = 0; i < UNR; ++i) {
+                    const int h = h0 + i * R + g;
+                    const int id = __shfl_sync(FULL, hq, h & 31);
+                    t[i] = (h < H) ? ldcg4(P.item_w + (size_t)id * D + 4 * sl) : f4zero();
+                }
+#pragma unroll
+                for (int i = 0; i < UNR; ++i) acc = acc + t[i];
+            }
+            acc = cross_sum4<VL>(acc);
+            const float rH = (float)(1.0 / (double)H);     // behavior_aggregators.cpp:63
+            const float4 mean = rH * acc;
+            float *ms = ring + (iter & 31) * 2 * D;
+            if (g == 0) *reinterpret_cast<float4 *>(ms + 4 * sl) = mean;
+            __syncwarp();
+
+            // ---- f = mean . W0 (behavior_aggregators.cpp:118), u <- gamma*u + (1-gamma)*f (:122)
+            float4 f = f4zero();
+#pragma unroll 4
+            for (int i4 = 0; i4 < IPG; i4 += 4) {
+                const float4 m4 = *reinterpret_cast<const float4 *>(ms + g * IPG + i4);
+                const float *wr = W0s + (g * IPG + i4) * D + 4 * sl;
+                fma4(f, m4.x, *reinterpret_cast<const float4 *>(wr));
+                fma4(f, m4.y, *reinterpret_cast<const float4 *>(wr + D));
+                fma4(f, m4.z, *reinterpret_cast<const float4 *>(wr + 2 * D));
+                fma4(f, m4.w, *reinterpret_cast<const float4 *>(wr + 3 * D));
+            }
+            f = cross_sum4<VL>(f);
+            float4 ua = make_float4(gamma * uw.x + omg * f.x, gamma * uw.y + omg * f.y,
+                                    gamma * uw.z + omg * f.z, gamma * uw.w + omg * f.w);
+
+            // ---- positive pair (matrix_factorization.cpp:45-63)
+            const float uu = group_sum<VL>(dot4(ua, ua));
+            const float pp = group_sum<VL>(dot4(pw, pw));
+            const float upd = group_sum<VL>(dot4(ua, pw));
+            const float unorm = sqrtf(fmaxf(uu, eps)), pnorm = sqrtf(fmaxf(pp, eps));
+            const float unorm3 = unorm * unorm * unorm, pnorm3 = pnorm * pnorm * pnorm;
+            const float r_u3_p = 1.f / (unorm3 * pnorm), r_u_p3 = 1.f / (unorm * pnorm3);
+            const float4 gu_p = r_u3_p * (uu * pw - upd * ua);
+            const float4 gp_p = (-r_u_p3) * (pp * ua - upd * pw);
+            const float cos_p = upd / (unorm * pnorm);
+
+            // ---- negatives: dots, scores, softmax loss (matrix_factorization.cpp:82-109)
+            float un[NJ], nn[NJ], nnorm[NJ], sc[NJ];
+            float m = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) {
+                un[j] = group_sum<VL>(dot4(ua, nw[j]));
+                nn[j] = group_sum<VL>(dot4(nw[j], nw[j]));
+                nnorm[j] = sqrtf(nn[j] < eps ? eps : nn[j]);
+                sc[j] = (j * R + g < K) ? (un[j] / (unorm * nnorm[j]) - cos_p) * score_mul : -INFINITY;
+                m = fmaxf(m, sc[j]);
+            }
+            m = cross_max<VL>(m);
+            float esum = 0.f;
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) { sc[j] = expf(sc[j] - m); esum += sc[j]; }
+            esum = cross_sum<VL>(esum);
+            esum += expf(-m);                                  // the implicit zero logit (:107)
+            const float loss = m + logf(esum);                 // :108
+            const float inv_esum = 1.f / esum;
+
+            // ---- backward (matrix_factorization.cpp:118-150)
+            float4 gacc = f4zero();
+            float lgsum = 0.f;
+            if (!dup) {
+#pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    if (j * R + g < K) {
+                        const float lg = (sc[j] * inv_esum) * score_mul;            // :109
+                        const float nnorm3 = nnorm[j] * nnorm[j] * nnorm[j];
+                        const float r_u3_n = 1.f / (unorm3 * nnorm[j]), r_u_n3 = 1.f / (unorm * nnorm3);
+                        const float4 gu_n = r_u3_n * (uu * nw[j] - un[j] * ua);     // :138
+                        const float4 gn_n = r_u_n3 * (nn[j] * ua - un[j] * nw[j]);  // :139
+                        fma4(gacc, lg, gu_n - gu_p);                                 // :141
+                        lgsum += lg;                                                 // :142
+                        float *grow = P.item_g + (size_t)nid[j] * D + 4 * sl;
+                        float4 gk = PRELOAD_G ? gn[j] : ldcg4(grow);
+                        fma4(gk, lg, gn_n);                                          // :143
+                        gk = clamp4(gk, P.clip);                                     // sgd.cpp:21-25
+                        fma4(nw[j], -P.lr, gk);
+                        stcg4(P.item_w + (size_t)nid[j] * D + 4 * sl, nw[j]);        // :148
+                        stcg4(grow, gk);                                             // :149
+                    }
+                }
+            } else {
+                // Duplicate negative ids in this sample: replay the reference's sequential k loop
+                // (grad row re-read per k, last writer wins on the weight row).
+#pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+#pragma unroll
+                    for (int gg = 0; gg < R; ++gg) {
+                        if (gg == g && j * R + g < K) {
+                            const float lg = (sc[j] * inv_esum) * score_mul;
+                            const float nnorm3 = nnorm[j] * nnorm[j] * nnorm[j];
+                            const float r_u3_n = 1.f / (unorm3 * nnorm[j]), r_u_n3 = 1.f / (unorm * nnorm3);
+                            const float4 gu_n = r_u3_n * (uu * nw[j] - un[j] * ua);
+                            const float4 gn_n = r_u_n3 * (nn[j] * ua - un[j] * nw[j]);
+                            fma4(gacc, lg, gu_n - gu_p);
+                            lgsum += lg;
+                            float *grow = P.item_g + (size_t)nid[j] * D + 4 * sl;
+                            float4 gk = ldcg4(grow);
+                            fma4(gk, lg, gn_n);
+                            gk = clamp4(gk, P.clip);
+                            float4 nk = nw[j];
+                            fma4(nk, -P.lr, gk);
+                            stcg4(P.item_w + (size_t)nid[j] * D + 4 * sl, nk);
+                            stcg4(grow, gk);
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+            gacc = cross_sum4<VL>(gacc);
+            lgsum = cross_sum<VL>(lgsum);
+            float4 gu = gu_old + gacc;
+            float4 gp = gp_old;
+            fma4(gp, lgsum, gp_p);
+
+            // ---- aggregator backward (behavior_aggregators.cpp:129-153)
+            if (g == 0) *reinterpret_cast<float4 *>(ms + D + 4 * sl) = omg * gu;
+            iter += 1;                                         // forward's iteration += 1 (:124)
+            __syncwarp();
+            if ((iter & 31) == 0) { w0_flush<D>(ring, W0s, P.w0, 32, P.lr_w0, lane); __syncwarp(); }
+            gu = gamma * gu;
+
+            // ---- user / positive step and write-back (matrix_factorization.cpp:166-174)
+            gu = clamp4(gu, P.clip);
+            fma4(ua, -P.lr, gu);
+            gp = clamp4(gp, P.clip);
+            fma4(pw, -P.lr, gp);
+            if (R == 1 || g == 0) {
+                stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
+                stcg4(P.item_w + (size_t)p * D + 4 * sl, pw);
+            }
+            if (R == 1 || g == 1) {
+                stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
+                stcg4(P.item_g + (size_t)p * D + 4 * sl, gp);
+            }
+            if (P.loss_out && lane == 0) P.loss_out[s - P.begin] = loss;
+            loss_acc += (double)loss;
+        }
+    }
+    __syncwarp();
+    if (!P.drop_w0_tail && (iter & 31) != 0) w0_flush<D>(ring, W0s, P.w0, (int)(iter & 31), P.lr_w0, lane);
+    if (lane == 0 && loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
+}
+
+}  // namespace heat

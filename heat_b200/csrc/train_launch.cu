@@ -1,0 +1,102 @@
+// heat_b200/csrc/train_launch.cu -- instantiates and launches the fused training kernel.
+#include "heat_ctx.cuh"
+#include "train_kernel.cuh"
+
+namespace heat {
+
+namespace {
+
+template <int D, int NJ, int WARPS, bool PRELOAD_G>
+int launch_one(Ctx *c, const TrainParams &P, int blocks)
+{
+    auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G>;
+    const size_t smem = (size_t)(D * D + WARPS * 32 * 2 * D) * sizeof(float);
+    HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
+    kern<<<blocks, WARPS * 32, smem, c->stream>>>(P);
+    HEAT_CUDA(cudaGetLastError());
+    HEAT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+// Pick the instantiation for (D, K, warps).  K must fit the register-resident path:
+// K <= NJ * 32/(D/4).
+int dispatch(Ctx *c, const TrainParams &P, bool deterministic)
+{
+    const int D = (int)c->cfg.emb_dim, K = P.K;
+    int warps = (int)c->cfg.warps_per_block;
+    const int bps = c->cfg.blocks_per_sm ? (int)c->cfg.blocks_per_sm : 1;
+    const int blocks = deterministic ? 1 : c->num_sms * bps;
+#define HEAT_LAUNCH(D_, NJ_, W_, PG_) return launch_one<D_, NJ_, W_, PG_>(c, P, blocks)
+    if (D == 64 && K <= 16) {
+        if (deterministic) HEAT_LAUNCH(64, 8, 1, true);
+        if (warps == 0) warps = 12;
+        if (warps <= 4) HEAT_LAUNCH(64, 8, 4, true);
+        if (warps <= 8) HEAT_LAUNCH(64, 8, 8, true);
+        HEAT_LAUNCH(64, 8, 12, true);
+    }
+    if (D == 64 && K <= 32) {
+        if (deterministic) HEAT_LAUNCH(64, 16, 1, false);
+        HEAT_LAUNCH(64, 16, 8, false);
+    }
+    if (D == 128 && K <= 16) {
+        if (deterministic) HEAT_LAUNCH(128, 16, 1, false);
+        HEAT_LAUNCH(128, 16, 4, false);
+    }
+    if (D == 32 && K <= 32) {
+        if (deterministic) HEAT_LAUNCH(32, 8, 1, true);
+        HEAT_LAUNCH(32, 8, 8, true);
+    }
+#undef HEAT_LAUNCH
+    return fail("unsupported (emb_dim, num_negs) = (" + std::to_string(D) + ", " + std::to_string(K) +
+                "): the register-resident kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16");
+}
+
+}  // namespace
+
+int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host)
+{
+    if (!c->clicks) return fail("heat_set_dataset has not been called");
+    if (!c->user_w) return fail("heat_bind_tables has not been called");
+    if (end > c->n_samples || begin > end) return fail("sample range out of bounds");
+    if (c->max_his > 128) return fail("max_his > 128 is not supported by the training kernel");
+    if (loss_sum_host) *loss_sum_host = 0.0;
+    if (begin == end) { c->last_kernel_ms = 0.f; return 0; }
+
+    float *d_loss_out = nullptr;
+    if (loss_per_sample_host) HEAT_CUDA(cudaMalloc(&d_loss_out, (end - begin) * sizeof(float)));
+    HEAT_CUDA(cudaMemsetAsync(c->chunk_counter, 0, sizeof(unsigned long long), c->stream));
+    HEAT_CUDA(cudaMemsetAsync(c->loss_sum, 0, sizeof(double), c->stream));
+
+    TrainParams P{};
+    P.clicks = c->clicks; P.his = c->his; P.masks = c->masks;
+    P.user_w = c->user_w; P.item_w = c->item_w; P.user_g = c->user_g; P.item_g = c->item_g; P.w0 = c->w0;
+    P.chunk_counter = c->chunk_counter; P.loss_sum = c->loss_sum; P.loss_out = d_loss_out;
+    P.begin = (long long)begin; P.end = (long long)end;
+    P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed;
+    P.epoch = (unsigned)c->epoch;
+    P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
+    P.chunk = (int)c->cfg.chunk;
+    P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
+    P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
+
+    int rc = dispatch(c, P, c->cfg.deterministic != 0);
+    if (rc == 0) {
+        double loss = 0.0;
+        cudaError_t e = cudaMemcpyAsync(&loss, c->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess && loss_per_sample_host)
+            e = cudaMemcpyAsync(loss_per_sample_host, d_loss_out, (end - begin) * sizeof(float),
+                                cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = fail(std::string("training kernel: ") + cudaGetErrorString(e));
+        else {
+            cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1);
+            if (loss_sum_host) *loss_sum_host = loss;
+        }
+    }
+    if (d_loss_out) cudaFree(d_loss_out);
+    return rc;
+}
+
+}  // namespace heat

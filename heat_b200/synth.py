@@ -1,0 +1,180 @@
+"""Seeded synthetic click datasets at the BASELINE.json shapes.
+
+The reference trains on LightGCN-format files (``user item item ...`` per line,
+cf_cpu/cf/datasets.py:31-40) that are not available offline, so every test and
+benchmark uses data of the same SHAPE generated here: power-law item popularity,
+log-normal user degrees, and a planted cluster structure so that Recall@k is
+non-trivial.  The history/mask arrays follow cf_cpu/cf/datasets.py:47-61 exactly
+(``random.sample`` when a user has >= max_his items, else pad with the last item).
+
+Nothing here is on the timed path; it only produces the host arrays that the
+reference frontend would hand to ``cf_c`` (uint64 clicks [N,2], his_items
+[U,max_his], masks [U,1]; float32 tables initialised N(0, 1e-2), models.py:15-16).
+"""
+from __future__ import annotations
+
+import dataclasses
+import random as _pyrandom
+
+import numpy as np
+
+# (users, items, train interactions) -- BASELINE.json configs / SURVEY.md 8.0
+SHAPES = {
+    "gowalla": (29858, 40981, 810128),
+    "yelp18": (31668, 38048, 1237259),
+    "amazon-book": (52643, 91599, 2380730),
+    "tiny": (200, 300, 4000),
+    "small": (2000, 3000, 60000),
+}
+
+
+@dataclasses.dataclass
+class ClickData:
+    num_users: int
+    num_items: int
+    max_his: int
+    clicks: np.ndarray        # [N, 2] uint64, file order (all of a user's samples consecutive)
+    his_items: np.ndarray     # [U, max_his] uint64
+    masks: np.ndarray         # [U, 1] uint64
+    train_indptr: np.ndarray  # [U+1] int64  CSR of train items per user (for eval masking)
+    train_items: np.ndarray   # [N] int32
+    test_indptr: np.ndarray   # [U+1] int64
+    test_items: np.ndarray    # [T] int32
+
+    @property
+    def train_size(self) -> int:
+        return int(self.clicks.shape[0])
+
+
+def _degrees(rng, num_users, total, cap):
+    if num_users * cap < total or total < num_users:
+        raise ValueError(f"cannot place {total} interactions on {num_users} users with max degree {cap}")
+    raw = rng.lognormal(mean=0.0, sigma=1.0, size=num_users)
+    deg = np.maximum(1, np.floor(raw * (total / raw.sum())).astype(np.int64))
+    deg = np.minimum(deg, cap)
+    # fix the sum exactly: add/remove one interaction at a time from random users
+    diff = int(total - deg.sum())
+    for _guard in range(100000):
+        if diff == 0:
+            break
+        step = 1 if diff > 0 else -1
+        n = min(abs(diff), num_users)
+        idx = rng.choice(num_users, size=n, replace=False)
+        ok = (deg[idx] + step >= 1) & (deg[idx] + step <= cap)
+        deg[idx[ok]] += step
+        diff = int(total - deg.sum())
+    if diff != 0:
+        raise RuntimeError("degree fix-up did not converge")
+    return deg
+
+
+def generate(num_users: int, num_items: int, train_size: int, max_his: int = 100, seed: int = 2022,
+             test_frac: float = 0.2, n_clusters: int = 64, p_in: float = 0.8, zipf_a: float = 1.0,
+             max_degree: int | None = None) -> ClickData:
+    rng = np.random.default_rng(seed)
+    cap = max_degree if max_degree is not None else max(2, num_items // 8)
+    cap = min(cap, int(num_items * (1.0 - test_frac)) - 1)
+    deg_train = _degrees(rng, num_users, train_size, cap)
+    deg_test = np.maximum(1, np.rint(deg_train * (test_frac / (1.0 - test_frac))).astype(np.int64))
+    need = deg_train + deg_test
+
+    n_clusters = max(1, min(n_clusters, num_items // 4))
+    item_cluster = rng.integers(0, n_clusters, size=num_items)
+    user_cluster = rng.integers(0, n_clusters, size=num_users)
+    pop = 1.0 / (rng.permutation(num_items) + 10.0) ** zipf_a
+    glob_cdf = np.cumsum(pop)
+    order = np.argsort(item_cluster, kind="stable")          # items grouped by cluster
+    clus_cdf = np.cumsum(pop[order])
+    starts = np.searchsorted(item_cluster[order], np.arange(n_clusters), side="left")
+    ends = np.searchsorted(item_cluster[order], np.arange(n_clusters), side="right")
+    lo = np.where(starts > 0, clus_cdf[np.maximum(starts, 1) - 1], 0.0)
+    hi = clus_cdf[np.maximum(ends, 1) - 1]
+
+    chosen = [None] * num_users
+    pending = np.arange(num_users)
+    have = [np.empty(0, dtype=np.int64)] * num_users
+    for _round in range(8):
+        if pending.size == 0:
+            break
+        want = need[pending] - np.array([have[u].size for u in pending])
+        m = (want * 3) // 2 + 8
+        owner = np.repeat(pending, m)
+        r = rng.random(owner.size)
+        inside = rng.random(owner.size) < p_in
+        c = user_cluster[owner]
+        tgt = lo[c] + r * (hi[c] - lo[c])
+        pos_in = np.minimum(np.searchsorted(clus_cdf, tgt, side="right"), num_items - 1)
+        empty = ends[c] <= starts[c]
+        item_in = order[np.clip(pos_in, starts[c], np.maximum(ends[c] - 1, starts[c]))]
+        item_out = np.minimum(np.searchsorted(glob_cdf, r * glob_cdf[-1], side="right"), num_items - 1)
+        items = np.where(inside & ~empty, item_in, item_out).astype(np.int64)
+        off = np.concatenate([[0], np.cumsum(m)])
+        nxt = []
+        for j, u in enumerate(pending):
+            cand = np.concatenate([have[u], items[off[j]:off[j + 1]]])
+            _, first = np.unique(cand, return_index=True)
+            cand = cand[np.sort(first)]
+            if cand.size >= need[u]:
+                chosen[u] = cand[:need[u]]
+            else:
+                have[u] = cand
+                nxt.append(u)
+        pending = np.array(nxt, dtype=np.int64)
+    for u in pending:  # extremely unlikely; fill with unused ids deterministically
+        used = set(have[u].tolist())
+        extra = [i for i in range(num_items) if i not in used][: need[u] - have[u].size]
+        chosen[u] = np.concatenate([have[u], np.array(extra, dtype=np.int64)])
+
+    train_indptr = np.concatenate([[0], np.cumsum(deg_train)]).astype(np.int64)
+    test_indptr = np.concatenate([[0], np.cumsum(deg_test)]).astype(np.int64)
+    train_items = np.concatenate([chosen[u][:deg_train[u]] for u in range(num_users)]).astype(np.int32)
+    test_items = np.concatenate([chosen[u][deg_train[u]:] for u in range(num_users)]).astype(np.int32)
+    clicks = np.empty((train_size, 2), dtype=np.uint64)
+    clicks[:, 0] = np.repeat(np.arange(num_users, dtype=np.uint64), deg_train)
+    clicks[:, 1] = train_items.astype(np.uint64)
+    his_items, masks = build_history(train_indptr, train_items, max_his, seed)
+    return ClickData(num_users, num_items, max_his, clicks, his_items, masks,
+                     train_indptr, train_items, test_indptr, test_items)
+
+
+def build_history(train_indptr, train_items, max_his: int, seed: int):
+    """cf_cpu/cf/datasets.py:47-61 with a seeded ``random`` (the reference leaves it unseeded)."""
+    rnd = _pyrandom.Random(seed)
+    num_users = train_indptr.size - 1
+    his = np.zeros((num_users, max_his), dtype=np.uint64)
+    masks = np.zeros((num_users, 1), dtype=np.uint64)
+    for u in range(num_users):
+        items = train_items[train_indptr[u]:train_indptr[u + 1]]
+        n = items.size
+        if n >= max_his:
+            his[u] = rnd.sample(items.tolist(), max_his)
+            masks[u, 0] = max_his
+        elif n > 0:
+            his[u, :n] = items
+            his[u, n:] = items[-1]
+            masks[u, 0] = n
+    return his, masks
+
+
+def generate_named(name: str, max_his: int = 100, seed: int = 2022) -> ClickData:
+    u, i, n = SHAPES[name]
+    return generate(u, i, n, max_his=max_his, seed=seed)
+
+
+def init_tables(num_users: int, num_items: int, emb_dim: int, seed: int = 2022):
+    """N(0, 1e-2^2) fp32 tables and W0 (models.py:15-16, behavior_aggregators.py:15), numpy-seeded."""
+    rng = np.random.default_rng(seed + 1)
+    user_w = (rng.standard_normal((num_users, emb_dim)) * 1e-2).astype(np.float32)
+    item_w = (rng.standard_normal((num_items, emb_dim)) * 1e-2).astype(np.float32)
+    w0 = (rng.standard_normal((emb_dim, emb_dim)) * 1e-2).astype(np.float32)
+    return user_w, item_w, w0
+
+
+def write_lightgcn_txt(data: ClickData, train_path: str, test_path: str) -> None:
+    """Write ``user item item ...`` lines (the format cf_cpu/cf/datasets.py:31-40 parses)."""
+    for path, indptr, items in ((train_path, data.train_indptr, data.train_items),
+                                (test_path, data.test_indptr, data.test_items)):
+        with open(path, "w") as f:
+            for u in range(data.num_users):
+                row = items[indptr[u]:indptr[u + 1]]
+                f.write(" ".join([str(u)] + [str(int(x)) for x in row]) + "\n")

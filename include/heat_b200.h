@@ -1,0 +1,158 @@
+/* include/heat_b200.h -- C ABI of the B200-native HEAT MF_CCL hot path.
+ *
+ * Drop-in boundary: the reference sits behind the pybind11 module `cf_c`
+ * (cf_cpu/src/pybind/init_modules.cpp:13-152).  The host C++ classes that module binds
+ * (heat_b200/csrc/host/) keep the reference's names and semantics and reach the GPU only
+ * through the entry points declared here: plain pointers and sizes, no torch / pybind /
+ * CUDA types.  Each entry point names the reference interface it replaces.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure;
+ * heat_last_error() returns a thread-local message for the last failure.  A context is
+ * bound to one CUDA device (one process per GPU); calls on one context are not
+ * thread-safe.  There is NO CPU fallback: without a usable CUDA device heat_create fails.
+ */
+#ifndef HEAT_B200_H
+#define HEAT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HEAT_ABI_VERSION 1
+
+typedef struct heat_ctx heat_ctx;
+
+/* Mirrors cf::modules::CFConfig (cf_cpu/src/modules/cf_config.hpp:12-35; python kwargs at
+ * init_modules.cpp:17-30) plus the knobs the GPU path adds.  Zero in an extension field
+ * selects the documented default, so a memset-0 struct with the reference fields filled
+ * in is a valid configuration. */
+typedef struct heat_config {
+    /* --- reference fields --- */
+    uint64_t emb_dim;           /* D: 32, 64 or 128 */
+    uint64_t num_negs;          /* K */
+    uint64_t num_users;         /* rows of the (local) user table */
+    uint64_t num_items;
+    uint64_t train_size;        /* N local samples */
+    uint64_t neg_sampler;       /* 0 uniform, 1 random-tile (same draws in the shipped loop: SURVEY 8.1 a4) */
+    uint64_t tile_size;
+    uint64_t refresh_interval;
+    uint64_t num_subepochs;     /* fork-only; accepted and ignored */
+    float l2;                   /* read, never applied (matrix_factorization.cpp:126,146,165,168) */
+    float clip_val;
+    float l_r;
+    const uint64_t *milestones; /* copied */
+    uint64_t n_milestones;
+    /* --- extensions --- */
+    uint64_t seed;              /* Philox key; default 2022 (the YAMLs' seed) */
+    uint64_t sample_offset;     /* global index of local sample 0 (multi-GPU shards) */
+    uint32_t chunk;             /* samples a warp takes per scheduling step; default 64
+                                   (the reference's omp schedule(dynamic,512), engine.cpp:327) */
+    uint32_t deterministic;     /* 1: one warp walks the samples in file order (== 1 OpenMP thread) */
+    uint32_t w0_tail_mode;      /* 0 default: per-warp W0 grads left over at launch end are applied
+                                   (scaled 1/32); 1: dropped like the reference's per-thread
+                                   aggregator at epoch end (behavior_aggregators.cpp:141-146) */
+    uint32_t warps_per_block;   /* 0 = tuned default */
+    uint32_t blocks_per_sm;     /* 0 = tuned default */
+    uint32_t reserved0;
+} heat_config;
+
+/* ---- life cycle -------------------------------------------------------------------- */
+int heat_abi_version(void);
+const char *heat_last_error(void);
+/* replaces: cf_c.modules.CFConfig(...) + Engine ctor (engine.cpp:9-20) */
+int heat_create(heat_ctx **out, const heat_config *cfg, int device);
+int heat_destroy(heat_ctx *ctx);
+
+/* ---- inputs ------------------------------------------------------------------------ */
+/* replaces: cf_c.modules.datasets.ClickDataset(click_dataset, historical_items, masks)
+ * (init_modules.cpp:45-61; dataset.cpp:10-19).  Host uint64 arrays in the reference's
+ * layout: clicks [n,2], his_items [num_users,max_his], masks [num_users,1].  Copied to the
+ * device and narrowed to int32 there; the host arrays are not retained. */
+int heat_set_dataset(heat_ctx *ctx, const uint64_t *clicks, uint64_t n,
+                     const uint64_t *his_items, uint64_t num_users, uint64_t max_his,
+                     const uint64_t *masks);
+/* replaces: cf_c.modules.models.MatrixFactorization(cf_config, user_weights, item_weights)
+ * and behavior_aggregators.AggregatorWeights(aggregator_weights0) (init_modules.cpp:74-84,
+ * 95-98).  The reference aliases these host buffers and trains them in place; here they
+ * are uploaded, the pointers are retained, and heat_sync_to_host writes the trained
+ * tables back into them. */
+int heat_bind_tables(heat_ctx *ctx, float *user_w, float *item_w, float *w0);
+int heat_upload_tables(heat_ctx *ctx);   /* host -> device again (after the caller edited them) */
+int heat_sync_to_host(heat_ctx *ctx);    /* device -> the bound host buffers */
+
+/* ---- training ---------------------------------------------------------------------- */
+/* replaces: Engine::train_one_epoch() (upstream loop, engine.cpp:156-160,293-347,378-385):
+ * LR schedule, all N local samples in file order through the fused kernel, zero_grad,
+ * epoch += 1.  *mean_loss = sum(loss) / N. */
+int heat_train_epoch(heat_ctx *ctx, double *mean_loss);
+/* The same kernel over local samples [begin,end) without the epoch bookkeeping (no LR
+ * schedule, no zero_grad, epoch counter unchanged).  loss_per_sample may be NULL or a
+ * host array of (end-begin) floats. */
+int heat_train_range(heat_ctx *ctx, uint64_t begin, uint64_t end, double *loss_sum,
+                     float *loss_per_sample);
+int heat_zero_grad(heat_ctx *ctx);                       /* embedding.cpp:41-45 */
+int heat_get_grads(heat_ctx *ctx, float *user_g, float *item_g);   /* either may be NULL */
+int heat_set_lr(heat_ctx *ctx, float l_r);
+int heat_get_lr(heat_ctx *ctx, float *l_r);
+int heat_get_epoch(heat_ctx *ctx, uint64_t *epoch);
+int heat_set_epoch(heat_ctx *ctx, uint64_t epoch);
+/* device time of the last heat_train_epoch / heat_train_range kernel, CUDA events, ms */
+int heat_last_kernel_ms(heat_ctx *ctx, float *ms);
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+int heat_launch_count(heat_ctx *ctx, uint64_t *n);
+
+/* ---- index contracts (bit-exact tests) --------------------------------------------- */
+/* Negative ids the device sampler draws for local samples [begin,end) of `epoch`:
+ * out[(s-begin)*K + k].  replaces: UniformRandomNegativeSampler::ignore_pos_sampling
+ * (uniform_random_negative_sampler.cpp:26-36). */
+int heat_sample_negatives(heat_ctx *ctx, uint64_t epoch, uint64_t begin, uint64_t end, uint64_t *out);
+/* Item ids the history aggregation gathers for local samples [begin,end):
+ * out_ids[(s-begin)*max_his + j] for j < out_count[s-begin], rest = UINT64_MAX.
+ * replaces: BehaviorAggregator::forward index reads (behavior_aggregators.cpp:60-62,96-99). */
+int heat_history_indices(heat_ctx *ctx, uint64_t begin, uint64_t end, uint64_t *out_ids, uint64_t *out_count);
+/* Host twin of the sampler (no GPU needed): one raw draw / one slot after look-back. */
+uint64_t heat_philox_draw(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k, uint64_t num_items);
+
+/* ---- evaluation -------------------------------------------------------------------- */
+/* replaces: Engine::evaluate0() + the copying binding lambda (engine.cpp:388-400,
+ * init_modules.cpp:122-129): out[U*I] = U . I^T (row-major, fp32 result). */
+int heat_eval_dense(heat_ctx *ctx, float *out);
+/* replaces: metrics.evaluate_metrics masking + argpartition/argsort (cf/metrics.py:21-29):
+ * score GEMM fused with a per-user masked top-k; the score matrix is never stored.
+ * train_indptr [U+1] / train_items: CSR of items to mask per user (may be NULL = no mask).
+ * topk_ids [U*k] int32 (sorted by score desc, ties to the smaller id), topk_scores [U*k]. */
+int heat_eval_topk(heat_ctx *ctx, uint32_t k, const int64_t *train_indptr, const int32_t *train_items,
+                   int32_t *topk_ids, float *topk_scores);
+/* replaces: Recall / NDCG / HitRate (cf/metrics.py:39-48,87-113,131-139) at k = 20 and 50,
+ * averaged over users with at least one test item.  out[6] = Recall@20, Recall@50,
+ * NDCG@20, NDCG@50, HitRate@20, HitRate@50; sums_out (may be NULL) receives the six
+ * un-normalised sums followed by the evaluated-user count (for multi-GPU reduction). */
+int heat_eval_metrics(heat_ctx *ctx, const int64_t *train_indptr, const int32_t *train_items,
+                      const int64_t *test_indptr, const int32_t *test_items,
+                      double out[6], double sums_out[7]);
+int heat_last_eval_ms(heat_ctx *ctx, float *ms);
+
+/* ---- multi-GPU (one process per GPU; NCCL over NVLink) -------------------------------- */
+/* 128-byte ncclUniqueId made by rank 0 and handed to every rank by the launcher. */
+int heat_comm_unique_id(uint8_t out[128]);
+int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[128]);
+/* replaces: the fork's per-row MPI_Bcast / MPI_Allreduce of item rows and the W0 average
+ * (engine.cpp:148-152,262-286,354-375): one all-reduce of the item-table delta and one of
+ * the W0 delta since the last sync; every rank ends with base + sum of deltas. */
+int heat_comm_sync_items(heat_ctx *ctx);
+int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);   /* 0 = once per epoch */
+
+/* ---- measurement helpers ------------------------------------------------------------ */
+/* L2-resident row gather/scatter micro-benchmark used as the L2 roofline denominator:
+ * random 256-byte rows of a `bytes`-sized buffer are read and rewritten. GB/s (read+write). */
+int heat_probe_l2_bandwidth(int device, uint64_t bytes, int iters, double *gbps);
+/* page-locked host memory for the end-to-end path */
+int heat_host_alloc(void **ptr, uint64_t bytes);
+int heat_host_free(void *ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HEAT_B200_H */

@@ -1,0 +1,40 @@
+"""CPU checks of the C-ABI library: it loads, exports every declared symbol, its host sampler twin
+agrees with the oracle, and it refuses to run without a GPU (no fallback)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from heat_b200 import abi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "heat_b200.h")).read()
+    declared = set(re.findall(r"\b(heat_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"heat_ctx", "heat_config"}
+    assert declared == set(abi.SYMBOLS), declared ^ set(abi.SYMBOLS)
+    L = abi.lib()
+    for s in declared:
+        assert hasattr(L, s), s
+    assert L.heat_abi_version() == 1
+
+
+def test_host_sampler_twin_matches_oracle():
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        seed, ep, s = int(rng.integers(1, 2**62)), int(rng.integers(0, 100)), int(rng.integers(0, 2**40))
+        k, n = int(rng.integers(0, 64)), int(rng.integers(1, 2**31 - 1))
+        r = oracle.philox4x32_10([s & 0xffffffff, s >> 32, ep, k >> 2], [seed & 0xffffffff, seed >> 32])[k & 3]
+        assert abi.philox_draw(seed, ep, s, k, n) == (r * n) >> 32
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(abi.HeatError, match="no CPU fallback"):
+        abi.Context(64, 16, 10, 10)

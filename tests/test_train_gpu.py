@@ -1,0 +1,208 @@
+"""GPU parity tests of the training path, through the C ABI, against the oracle / golden vectors."""
+import numpy as np
+import pytest
+
+import oracle
+from heat_b200 import abi, synth
+from helpers import TRAIN_CASES, fresh_tables, load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def make_ctx(g, **kw):
+    U, D = g["init_user_w"].shape
+    I = g["init_item_w"].shape[0]
+    ctx = abi.Context(D, int(g["K"]), U, I, clip_val=float(g["clip"]), l_r=float(g["lr"]), seed=int(g["seed"]), **kw)
+    ctx.set_dataset(g["clicks"], g["his_items"], g["masks"])
+    return ctx
+
+
+@pytest.mark.parametrize("name", TRAIN_CASES)
+@pytest.mark.parametrize("epoch,offset", [(0, 0), (3, 0), (1, 123456789012)])
+def test_sampler_bit_exact(name, epoch, offset):
+    g = load_golden(name)
+    I = g["init_item_w"].shape[0]
+    ctx = make_ctx(g, sample_offset=offset)
+    N = g["clicks"].shape[0]
+    dev = ctx.sample_negatives(epoch, 0, N)
+    ref = oracle.neg_table(int(g["seed"]), epoch, offset, g["clicks"], int(g["K"]), I)
+    assert np.array_equal(dev, ref)
+    if epoch == 0 and offset == 0:
+        assert np.array_equal(dev, g["negs"])
+    part = ctx.sample_negatives(epoch, 17, 101)
+    assert np.array_equal(part, ref[17:101])
+
+
+@pytest.mark.parametrize("name", TRAIN_CASES)
+def test_history_gather_indices_bit_exact(name):
+    g = load_golden(name)
+    ctx = make_ctx(g)
+    N = g["clicks"].shape[0]
+    ids, cnt = ctx.history_indices(0, N)
+    users = g["clicks"][:, 0].astype(np.int64)
+    H = g["masks"][users, 0]
+    assert np.array_equal(cnt, H)
+    want = g["his_items"][users].copy()
+    want[np.arange(want.shape[1])[None, :] >= H[:, None]] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    assert np.array_equal(ids, want)
+
+
+@pytest.mark.parametrize("name", TRAIN_CASES)
+@pytest.mark.parametrize("steps", [1, 3])
+def test_steps_match_reference_golden(name, steps):
+    g = load_golden(name)
+    uw, iw, w0 = fresh_tables(g)
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1)
+    ctx.bind_tables(uw, iw, w0)
+    total, per = ctx.train_range(0, steps, per_sample=True)
+    ctx.sync_to_host()
+    gu, gi = ctx.grads()
+    t = f"s{steps}_"
+    tol = 1e-5 if steps == 1 else 2e-4
+    assert np.allclose(per, g["losses"][:steps], rtol=10 * tol, atol=1e-5), (per, g["losses"][:steps])
+    assert abs(total - float(np.sum(g["losses"][:steps].astype(np.float64)))) < 1e-4 * steps
+    for got, key in ((uw, "user_w"), (iw, "item_w"), (w0, "w0"), (gu, "user_g"), (gi, "item_g")):
+        lim = tol * (10 if key.endswith("_g") else 1)
+        assert rel_err(got, g[t + key]) < lim, (key, rel_err(got, g[t + key]))
+
+
+@pytest.mark.parametrize("name", TRAIN_CASES)
+def test_each_sample_alone_matches_oracle(name):
+    """Teacher-forced: every one of the first 64 samples, applied alone to the SAME initial state,
+    must match the oracle's single step (covers duplicate negatives, draws equal to the positive,
+    short and full histories)."""
+    g = load_golden(name)
+    D, K = int(g["D"]), int(g["K"])
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1)
+    uw, iw, w0 = fresh_tables(g)
+    ctx.bind_tables(uw, iw, w0)
+    worst = 0.0
+    for s in range(64):
+        uw[:], iw[:], w0[:] = fresh_tables(g)
+        ctx.upload_tables(); ctx.zero_grad()
+        _, per = ctx.train_range(s, s + 1, per_sample=True)
+        ctx.sync_to_host()
+        a = fresh_tables(g)
+        o = oracle.COracle(D, K, g["clicks"], g["his_items"], g["masks"], *a, clip_val=float(g["clip"]), l_r=float(g["lr"]))
+        l = o.step(int(g["clicks"][s, 0]), int(g["clicks"][s, 1]), g["negs"][s])
+        o.close()
+        assert abs(per[0] - l) < 1e-4 * max(1.0, abs(l)), (s, per[0], l)
+        for got, ref in ((uw, a[0]), (iw, a[1])):
+            worst = max(worst, rel_err(got, ref))
+            assert rel_err(got, ref) < 1e-5, (s, rel_err(got, ref))
+    print(name, "worst single-step rel err", worst)
+
+
+@pytest.mark.parametrize("name", ["train_d64_k16", "train_d128_k16", "train_d32_k8"])
+def test_w0_update_with_frozen_tables(name):
+    """70 sequential samples with the table LR at 0: two W0 updates (iterations 32 and 64), the tail
+    dropped as the reference does; nothing chaotic, so the whole state must agree."""
+    g = load_golden(name)
+    D, K = int(g["D"]), int(g["K"])
+    uw, iw, w0 = fresh_tables(g)
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1)
+    ctx.bind_tables(uw, iw, w0)
+    ctx.set_lr(0.0)
+    _, per = ctx.train_range(0, 70, per_sample=True)
+    ctx.sync_to_host()
+    a = fresh_tables(g)
+    o = oracle.COracle(D, K, g["clicks"], g["his_items"], g["masks"], *a, clip_val=float(g["clip"]), l_r=float(g["lr"]))
+    o.set_lr(0.0)
+    ref = [o.step(int(g["clicks"][s, 0]), int(g["clicks"][s, 1]), g["negs"][s]) for s in range(70)]
+    assert np.allclose(per, ref, rtol=1e-4, atol=1e-5)
+    assert not np.array_equal(w0, g["init_w0"])
+    assert rel_err(w0, a[2]) < 1e-5, rel_err(w0, a[2])
+    assert rel_err(uw, a[0]) < 1e-5 and rel_err(iw, a[1]) < 1e-5
+
+
+def test_w0_tail_flush_applies_leftover():
+    g = load_golden("train_d64_k16")
+    outs = []
+    for mode in (0, 1):
+        uw, iw, w0 = fresh_tables(g)
+        ctx = make_ctx(g, deterministic=True, w0_tail_mode=mode)
+        ctx.bind_tables(uw, iw, w0); ctx.set_lr(0.0)
+        ctx.train_range(0, 20); ctx.sync_to_host()
+        outs.append(w0.copy())
+    assert np.array_equal(outs[1], g["init_w0"])        # dropped: fewer than 32 samples
+    assert not np.array_equal(outs[0], g["init_w0"])    # default: applied with the 1/32 scale
+
+
+def test_epoch_statistics_hogwild_vs_sequential_oracle():
+    d = synth.generate_named("small")
+    D, K = 64, 16
+    a = synth.init_tables(d.num_users, d.num_items, D)
+    b = synth.init_tables(d.num_users, d.num_items, D)
+    ctx = abi.Context(D, K, d.num_users, d.num_items)
+    ctx.set_dataset(d.clicks, d.his_items, d.masks); ctx.bind_tables(*a)
+    o = oracle.COracle(D, K, d.clicks, d.his_items, d.masks, *b)
+    for ep in range(3):
+        lg, lo = ctx.train_epoch(), o.train_epoch(nthreads=1)
+        print("epoch", ep, "gpu", lg, "oracle", lo)
+        assert np.isfinite(lg) and abs(lg - lo) / lo < 0.08, (ep, lg, lo)
+    ctx.sync_to_host()
+    gu, gi = ctx.grads()
+    assert not gu.any() and not gi.any()
+    assert ctx.get_epoch() == 3
+    for t in a:
+        assert np.isfinite(t).all()
+
+
+def test_deterministic_mode_is_reproducible_and_hogwild_is_close():
+    d = synth.generate_named("tiny")
+    D, K = 64, 16
+    runs = []
+    for _ in range(2):
+        t = synth.init_tables(d.num_users, d.num_items, D)
+        ctx = abi.Context(D, K, d.num_users, d.num_items, deterministic=True)
+        ctx.set_dataset(d.clicks, d.his_items, d.masks); ctx.bind_tables(*t)
+        runs.append((ctx.train_epoch(), ctx.train_epoch()))
+        ctx.sync_to_host(); runs.append(t[1].copy())
+    assert runs[0] == runs[2] and np.array_equal(runs[1], runs[3])
+
+
+def test_lr_schedule_and_bookkeeping():
+    d = synth.generate(40, 60, 400, max_his=10, n_clusters=2, max_degree=20)
+    t = synth.init_tables(40, 60, 32)
+    ctx = abi.Context(32, 8, 40, 60, milestones=(2,))
+    ctx.set_dataset(d.clicks, d.his_items, d.masks); ctx.bind_tables(*t)
+    lrs = []
+    for _ in range(5):
+        ctx.train_epoch(); lrs.append(ctx.get_lr())
+    assert np.allclose(lrs, [1e-2, 1e-2, 1e-3, 1e-3, 1e-4], rtol=1e-6)
+    assert ctx.launch_count() >= 5
+
+
+def test_errors_are_loud():
+    ctx = abi.Context(64, 16, 10, 10)
+    with pytest.raises(abi.HeatError):
+        ctx.train_epoch()                                  # no dataset
+    bad = np.array([[0, 11]], np.uint64)                   # item id out of range
+    with pytest.raises(abi.HeatError, match="out of range"):
+        ctx.set_dataset(bad, np.zeros((10, 4), np.uint64), np.ones((10, 1), np.uint64))
+    with pytest.raises(abi.HeatError, match="unsupported"):
+        c2 = abi.Context(48, 16, 10, 10)
+        c2.set_dataset(np.array([[0, 1]], np.uint64), np.zeros((10, 4), np.uint64), np.ones((10, 1), np.uint64))
+        c2.bind_tables(np.zeros((10, 48), np.float32), np.zeros((10, 48), np.float32), np.zeros((48, 48), np.float32))
+        c2.train_epoch()
+
+
+def test_full_size_amazon_shape_properties():
+    """BASELINE configs[2] shape: one Hogwild epoch, size-independent properties only."""
+    d = synth.generate_named("amazon-book")
+    D, K = 64, 16
+    t = synth.init_tables(d.num_users, d.num_items, D)
+    ctx = abi.Context(D, K, d.num_users, d.num_items)
+    ctx.set_dataset(d.clicks, d.his_items, d.masks); ctx.bind_tables(*t)
+    # index contracts at full size on a strided sample
+    negs = ctx.sample_negatives(0, 1000000, 1000512)
+    ref = oracle.neg_table(2022, 0, 0, d.clicks, K, d.num_items)[1000000:1000512] if False else None
+    sub = np.ascontiguousarray(d.clicks[:1000512])
+    assert np.array_equal(negs, oracle.neg_table(2022, 0, 0, sub, K, d.num_items)[1000000:])
+    l0 = ctx.train_epoch(); ms = ctx.last_kernel_ms()
+    l1 = ctx.train_epoch()
+    print("amazon-shape epoch loss", l0, l1, "kernel ms", ms, "samples/s", d.train_size / ms * 1e3)
+    assert np.isfinite(l0) and np.isfinite(l1) and l1 < l0 < np.log(K + 1) * 1.5
+    ctx.sync_to_host()
+    assert all(np.isfinite(x).all() for x in t)
+    assert ms < 2000.0     # the north-star's < 2 s epoch
