@@ -26,7 +26,7 @@ SYMBOLS = [
     "heat_abi_version", "heat_last_error", "heat_create", "heat_destroy", "heat_set_dataset",
     "heat_bind_tables", "heat_upload_tables", "heat_sync_to_host", "heat_train_epoch", "heat_train_range",
     "heat_zero_grad", "heat_get_grads", "heat_set_lr", "heat_get_lr", "heat_get_epoch", "heat_set_epoch",
-    "heat_last_kernel_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
+    "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval",
     "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free",
@@ -42,7 +42,8 @@ class HeatConfig(C.Structure):
         ("milestones", _u64p), ("n_milestones", C.c_uint64),
         ("seed", C.c_uint64), ("sample_offset", C.c_uint64),
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
-        ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("reserved0", C.c_uint32),
+        ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
+        ("reserved1", C.c_uint32), ("max_blocks", C.c_uint32),
     ]
 
 
@@ -76,6 +77,7 @@ def lib():
         L.heat_set_epoch.argtypes = [C.c_void_p, C.c_uint64]
         L.heat_last_kernel_ms.argtypes = [C.c_void_p, _f32p]
         L.heat_last_eval_ms.argtypes = [C.c_void_p, _f32p]
+        L.heat_last_epoch_ms.argtypes = [C.c_void_p, _f32p]
         L.heat_launch_count.argtypes = [C.c_void_p, _u64p]
         L.heat_sample_negatives.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, _u64p]
         L.heat_history_indices.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _u64p, _u64p]
@@ -140,7 +142,7 @@ class Context:
 
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
-                 warps_per_block=0, blocks_per_sm=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
+                 warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
                  device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
@@ -148,7 +150,8 @@ class Context:
                          refresh_interval=refresh_interval, num_subepochs=2, l2=l2, clip_val=clip_val, l_r=l_r,
                          milestones=_ptr(self._ms, _u64p), n_milestones=self._ms.size, seed=seed,
                          sample_offset=sample_offset, chunk=chunk, deterministic=int(bool(deterministic)),
-                         w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm)
+                         w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
+                         max_blocks=max_blocks, update_mode=update_mode)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0
@@ -220,6 +223,9 @@ class Context:
 
     def last_kernel_ms(self):
         v = C.c_float(); _ck(lib().heat_last_kernel_ms(self._h, C.byref(v))); return v.value
+
+    def last_epoch_ms(self):
+        v = C.c_float(); _ck(lib().heat_last_epoch_ms(self._h, C.byref(v))); return v.value
 
     def last_eval_ms(self):
         v = C.c_float(); _ck(lib().heat_last_eval_ms(self._h, C.byref(v))); return v.value

@@ -107,6 +107,8 @@ int heat_create(heat_ctx **out, const heat_config *cfg, int device)
     HEAT_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     HEAT_CUDA(cudaEventCreate(&c->ev0));
     HEAT_CUDA(cudaEventCreate(&c->ev1));
+    HEAT_CUDA(cudaEventCreate(&c->ev_e0));
+    HEAT_CUDA(cudaEventCreate(&c->ev_e1));
     HEAT_CUDA(cudaMalloc(&c->chunk_counter, sizeof(unsigned long long)));
     HEAT_CUDA(cudaMalloc(&c->loss_sum, sizeof(double)));
     *out = reinterpret_cast<heat_ctx *>(c);
@@ -123,6 +125,8 @@ int heat_destroy(heat_ctx *ctx)
     cudaFree(c->chunk_counter); cudaFree(c->loss_sum); cudaFree(c->eval_scratch);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_e0) cudaEventDestroy(c->ev_e0);
+    if (c->ev_e1) cudaEventDestroy(c->ev_e1);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return 0;
@@ -227,6 +231,7 @@ int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
         if (c->epoch > 0 && c->epoch % c->milestones[0] == 0) c->l_r = c->l_r * 0.1f;
     }
     const uint64_t N = c->n_samples;
+    HEAT_CUDA(cudaEventRecord(c->ev_e0, c->stream));
     double total = 0.0;
     float ms_total = 0.f;
     const uint64_t step = (c->world > 1 && c->sync_interval) ? c->sync_interval : N;
@@ -241,7 +246,9 @@ int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
     c->last_kernel_ms = ms_total;
     int rc = heat_zero_grad(ctx);                       // engine.cpp:345-347
     if (rc) return rc;
+    HEAT_CUDA(cudaEventRecord(c->ev_e1, c->stream));
     HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_epoch_ms, c->ev_e0, c->ev_e1);
     c->epoch += 1;                                      // engine.cpp:378
     if (mean_loss) *mean_loss = N ? total / (double)N : 0.0;
     return 0;
@@ -264,6 +271,7 @@ int heat_get_lr(heat_ctx *ctx, float *l_r) { Ctx *c = reinterpret_cast<Ctx *>(ct
 int heat_get_epoch(heat_ctx *ctx, uint64_t *epoch) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !epoch) return fail("null argument"); *epoch = c->epoch; return 0; }
 int heat_set_epoch(heat_ctx *ctx, uint64_t epoch) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c) return fail("null context"); c->epoch = epoch; return 0; }
 int heat_last_kernel_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_kernel_ms; return 0; }
+int heat_last_epoch_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_epoch_ms; return 0; }
 int heat_last_eval_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_eval_ms; return 0; }
 int heat_launch_count(heat_ctx *ctx, uint64_t *n) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !n) return fail("null argument"); *n = c->launches; return 0; }
 

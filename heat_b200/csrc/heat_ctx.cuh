@@ -19,7 +19,7 @@ struct Ctx {
     int device = 0;
     int num_sms = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_e0 = nullptr, ev_e1 = nullptr;
 
     int2 *clicks = nullptr;
     int *his = nullptr, *masks = nullptr;
@@ -31,7 +31,7 @@ struct Ctx {
 
     float l_r = 0.f;          // optimizer LR (scheduled); cfg.l_r stays the aggregator's LR
     uint64_t epoch = 0;
-    float last_kernel_ms = 0.f, last_eval_ms = 0.f;
+    float last_kernel_ms = 0.f, last_eval_ms = 0.f, last_epoch_ms = 0.f;
     uint64_t launches = 0;
 
     // multi-GPU

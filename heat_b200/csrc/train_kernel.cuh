@@ -40,13 +40,29 @@ struct TrainParams {
     unsigned long long sample_offset, seed;
     unsigned epoch;
     int max_his, num_items, K, chunk, drop_w0_tail;
+    int upd;                 // item-row update mode, see UPD_* below
     float lr, lr_w0, clip;
 };
 
 constexpr unsigned FULL = 0xffffffffu;
 
+// How a sample's item rows (positive + negatives: weight row and persistent grad row) are written back.
+//   UPD_STORE  the reference's own sequence (matrix_factorization.cpp:133-149,169-174): the row
+//              snapshot taken at gather time is stepped and stored.  Exact in sequential order;
+//              under thousands of concurrent warps the long read-modify-write window loses updates.
+//   UPD_FRESH  the rows are re-read immediately before the step, so the window shrinks from the
+//              whole sample (~9 us) to one L2 round trip.  Same result as UPD_STORE when nothing races.
+//   UPD_ATOMIC the step is applied as an L2 vector reduction (w += -lr*g_new, g += g_new - g_old):
+//              no update is ever lost, whatever the concurrency.
+enum { UPD_STORE = 0, UPD_FRESH = 1, UPD_ATOMIC = 2 };
+
 __device__ __forceinline__ float4 ldcg4(const float *p) { return __ldcg(reinterpret_cast<const float4 *>(p)); }
 __device__ __forceinline__ void stcg4(float *p, const float4 &v) { __stcg(reinterpret_cast<float4 *>(p), v); }
+// vector reduction at L2 (REDG.E.ADD.F32x4): the row update of the atomic Hogwild mode
+__device__ __forceinline__ void red4(float *p, const float4 &v)
+{
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 __device__ __forceinline__ float4 operator+(const float4 &a, const float4 &b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 __device__ __forceinline__ float4 operator-(const float4 &a, const float4 &b) { return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
@@ -156,7 +172,7 @@ __device__ __forceinline__ void w0_flush(const float *ring, float *W0s, float *w
 
 // D: embedding dim (32/64/128).  NJ: negative rows held per row group (K <= NJ * 32/(D/4)).
 // WARPS: warps per block.  PRELOAD_G: negative grad rows loaded up front with the weights.
-template <int D, int NJ, int WARPS, bool PRELOAD_G>
+template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD>
 __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams P)
 {
     constexpr int VL = D / 4;        // lanes per row
@@ -293,9 +309,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             // ---- backward (matrix_factorization.cpp:118-150)
             float4 gacc = f4zero();
             float lgsum = 0.f;
-            if (!dup) {
+            if (UPD != UPD_STORE || !dup) {
+                float4 dl[UPD == UPD_FRESH ? NJ : 1];
 #pragma unroll
                 for (int j = 0; j < NJ; ++j) {
+                    if (UPD == UPD_FRESH) dl[j] = f4zero();
                     if (j * R + g < K) {
                         const float lg = (sc[j] * inv_esum) * score_mul;            // :109
                         const float nnorm3 = nnorm[j] * nnorm[j] * nnorm[j];
@@ -304,13 +322,45 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
                         const float4 gn_n = r_u_n3 * (nn[j] * ua - un[j] * nw[j]);  // :139
                         fma4(gacc, lg, gu_n - gu_p);                                 // :141
                         lgsum += lg;                                                 // :142
+                        float *wrow = P.item_w + (size_t)nid[j] * D + 4 * sl;
                         float *grow = P.item_g + (size_t)nid[j] * D + 4 * sl;
-                        float4 gk = PRELOAD_G ? gn[j] : ldcg4(grow);
-                        fma4(gk, lg, gn_n);                                          // :143
-                        gk = clamp4(gk, P.clip);                                     // sgd.cpp:21-25
-                        fma4(nw[j], -P.lr, gk);
-                        stcg4(P.item_w + (size_t)nid[j] * D + 4 * sl, nw[j]);        // :148
-                        stcg4(grow, gk);                                             // :149
+                        if (UPD == UPD_FRESH) {
+                            dl[j] = lg * gn_n;
+                        } else {
+                            const float4 gold = PRELOAD_G ? gn[j] : ldcg4(grow);
+                            float4 gk = gold;
+                            fma4(gk, lg, gn_n);                                      // :143
+                            gk = clamp4(gk, P.clip);                                 // sgd.cpp:21-25
+                            if (UPD == UPD_ATOMIC) {
+                                red4(wrow, (-P.lr) * gk);
+                                red4(grow, gk - gold);
+                            } else {
+                                fma4(nw[j], -P.lr, gk);
+                                stcg4(wrow, nw[j]);                                  // :148
+                                stcg4(grow, gk);                                     // :149
+                            }
+                        }
+                    }
+                }
+                if (UPD == UPD_FRESH) {
+                    // second look at the rows, right before the step: all loads first, then the stores
+                    float4 fw[NJ], fg[NJ];
+#pragma unroll
+                    for (int j = 0; j < NJ; ++j) {
+                        if (j * R + g < K) {
+                            fw[j] = ldcg4(P.item_w + (size_t)nid[j] * D + 4 * sl);
+                            fg[j] = ldcg4(P.item_g + (size_t)nid[j] * D + 4 * sl);
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < NJ; ++j) {
+                        if (j * R + g < K) {
+                            float4 gk = fg[j] + dl[j];
+                            gk = clamp4(gk, P.clip);
+                            fma4(fw[j], -P.lr, gk);
+                            stcg4(P.item_w + (size_t)nid[j] * D + 4 * sl, fw[j]);
+                            stcg4(P.item_g + (size_t)nid[j] * D + 4 * sl, gk);
+                        }
                     }
                 }
             } else {
@@ -357,16 +407,28 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             // ---- user / positive step and write-back (matrix_factorization.cpp:166-174)
             gu = clamp4(gu, P.clip);
             fma4(ua, -P.lr, gu);
-            gp = clamp4(gp, P.clip);
-            fma4(pw, -P.lr, gp);
-            if (R == 1 || g == 0) {
-                stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
-                stcg4(P.item_w + (size_t)p * D + 4 * sl, pw);
+            float *prow = P.item_w + (size_t)p * D + 4 * sl, *pgrow = P.item_g + (size_t)p * D + 4 * sl;
+            if (UPD == UPD_STORE) {
+                gp = clamp4(gp, P.clip);
+                fma4(pw, -P.lr, gp);
+                if (R == 1 || g == 0) stcg4(prow, pw);
+                if (R == 1 || g == 1) stcg4(pgrow, gp);
+            } else if (UPD == UPD_ATOMIC) {
+                gp = clamp4(gp, P.clip);
+                if (R == 1 || g == 0) red4(prow, (-P.lr) * gp);
+                if (R == 1 || g == 1) red4(pgrow, gp - gp_old);
+            } else {
+                if (g == 0) {
+                    float4 fw = ldcg4(prow), fg = ldcg4(pgrow);
+                    fma4(fg, lgsum, gp_p);
+                    fg = clamp4(fg, P.clip);
+                    fma4(fw, -P.lr, fg);
+                    stcg4(prow, fw);
+                    stcg4(pgrow, fg);
+                }
             }
-            if (R == 1 || g == 1) {
-                stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
-                stcg4(P.item_g + (size_t)p * D + 4 * sl, gp);
-            }
+            if (R == 1 || g == 0) stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
+            if (R == 1 || g == 1) stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
             if (P.loss_out && lane == 0) P.loss_out[s - P.begin] = loss;
             loss_acc += (double)loss;
         }

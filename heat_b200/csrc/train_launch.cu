@@ -6,10 +6,10 @@ namespace heat {
 
 namespace {
 
-template <int D, int NJ, int WARPS, bool PRELOAD_G>
+template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD = UPD_STORE>
 int launch_one(Ctx *c, const TrainParams &P, int blocks)
 {
-    auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G>;
+    auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G, UPD>;
     const size_t smem = (size_t)(D * D + WARPS * 32 * 2 * D) * sizeof(float);
     HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
@@ -27,27 +27,37 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic)
     const int D = (int)c->cfg.emb_dim, K = P.K;
     int warps = (int)c->cfg.warps_per_block;
     const int bps = c->cfg.blocks_per_sm ? (int)c->cfg.blocks_per_sm : 1;
-    const int blocks = deterministic ? 1 : c->num_sms * bps;
+    int blocks = deterministic ? 1 : c->num_sms * bps;
+    if (c->cfg.max_blocks && blocks > (int)c->cfg.max_blocks) blocks = (int)c->cfg.max_blocks;
+    const int upd = deterministic ? (int)UPD_STORE : P.upd;
 #define HEAT_LAUNCH(D_, NJ_, W_, PG_) return launch_one<D_, NJ_, W_, PG_>(c, P, blocks)
+// Hogwild grid: the three item-row update modes of train_kernel.cuh
+#define HEAT_LAUNCH_UPD(D_, NJ_, W_, PG_)                                                   \
+    do {                                                                                    \
+        if (upd == UPD_ATOMIC) return launch_one<D_, NJ_, W_, PG_, UPD_ATOMIC>(c, P, blocks); \
+        if (upd == UPD_FRESH) return launch_one<D_, NJ_, W_, false, UPD_FRESH>(c, P, blocks); \
+        return launch_one<D_, NJ_, W_, PG_, UPD_STORE>(c, P, blocks);                       \
+    } while (0)
     if (D == 64 && K <= 16) {
         if (deterministic) HEAT_LAUNCH(64, 8, 1, true);
         if (warps == 0) warps = 12;
-        if (warps <= 4) HEAT_LAUNCH(64, 8, 4, true);
-        if (warps <= 8) HEAT_LAUNCH(64, 8, 8, true);
-        HEAT_LAUNCH(64, 8, 12, true);
+        if (warps <= 4) HEAT_LAUNCH_UPD(64, 8, 4, true);
+        if (warps <= 8) HEAT_LAUNCH_UPD(64, 8, 8, true);
+        HEAT_LAUNCH_UPD(64, 8, 12, true);
     }
     if (D == 64 && K <= 32) {
         if (deterministic) HEAT_LAUNCH(64, 16, 1, false);
-        HEAT_LAUNCH(64, 16, 8, false);
+        HEAT_LAUNCH_UPD(64, 16, 8, false);
     }
     if (D == 128 && K <= 16) {
         if (deterministic) HEAT_LAUNCH(128, 16, 1, false);
-        HEAT_LAUNCH(128, 16, 4, false);
+        HEAT_LAUNCH_UPD(128, 16, 4, false);
     }
     if (D == 32 && K <= 32) {
         if (deterministic) HEAT_LAUNCH(32, 8, 1, true);
-        HEAT_LAUNCH(32, 8, 8, true);
+        HEAT_LAUNCH_UPD(32, 8, 8, true);
     }
+#undef HEAT_LAUNCH_UPD
 #undef HEAT_LAUNCH
     return fail("unsupported (emb_dim, num_negs) = (" + std::to_string(D) + ", " + std::to_string(K) +
                 "): the register-resident kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16");
@@ -79,6 +89,7 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
     P.chunk = (int)c->cfg.chunk;
     P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
+    P.upd = (int)c->cfg.update_mode;
     P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
 
     int rc = dispatch(c, P, c->cfg.deterministic != 0);

@@ -55,7 +55,11 @@ typedef struct heat_config {
                                    aggregator at epoch end (behavior_aggregators.cpp:141-146) */
     uint32_t warps_per_block;   /* 0 = tuned default */
     uint32_t blocks_per_sm;     /* 0 = tuned default */
-    uint32_t reserved0;
+    uint32_t update_mode;       /* item-row write-back in the Hogwild grid: 0 store the stepped snapshot (the
+                                   reference's sequence), 1 re-read the rows right before the step, 2 apply the
+                                   step as L2 vector reductions (no lost updates). deterministic=1 forces 0 */
+    uint32_t reserved1;
+    uint32_t max_blocks;        /* 0 = one grid over all SMs; else cap on thread blocks (bounds Hogwild concurrency) */
 } heat_config;
 
 /* ---- life cycle -------------------------------------------------------------------- */
@@ -100,6 +104,8 @@ int heat_get_epoch(heat_ctx *ctx, uint64_t *epoch);
 int heat_set_epoch(heat_ctx *ctx, uint64_t epoch);
 /* device time of the last heat_train_epoch / heat_train_range kernel, CUDA events, ms */
 int heat_last_kernel_ms(heat_ctx *ctx, float *ms);
+/* device time of the whole last heat_train_epoch (kernel(s), zero_grad, item syncs), CUDA events, ms */
+int heat_last_epoch_ms(heat_ctx *ctx, float *ms);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 int heat_launch_count(heat_ctx *ctx, uint64_t *n);
 

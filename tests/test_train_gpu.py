@@ -133,7 +133,9 @@ def test_epoch_statistics_hogwild_vs_sequential_oracle():
     D, K = 64, 16
     a = synth.init_tables(d.num_users, d.num_items, D)
     b = synth.init_tables(d.num_users, d.num_items, D)
-    ctx = abi.Context(D, K, d.num_users, d.num_items)
+    # 8 warps in flight ~ the reference at 8 OpenMP threads: on a 3000-item table a full grid
+    # (1776 warps) would have every row in flight several times over, which no CPU run resembles
+    ctx = abi.Context(D, K, d.num_users, d.num_items, max_blocks=2, warps_per_block=4)
     ctx.set_dataset(d.clicks, d.his_items, d.masks); ctx.bind_tables(*a)
     o = oracle.COracle(D, K, d.clicks, d.his_items, d.masks, *b)
     for ep in range(3):
