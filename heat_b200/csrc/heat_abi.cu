@@ -122,7 +122,8 @@ int heat_destroy(heat_ctx *ctx)
     cudaSetDevice(c->device);
     comm_destroy(c);
     free_dataset(c); free_tables(c);
-    cudaFree(c->chunk_counter); cudaFree(c->loss_sum); cudaFree(c->eval_scratch);
+    eval_free(c);
+    cudaFree(c->chunk_counter); cudaFree(c->loss_sum);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_e0) cudaEventDestroy(c->ev_e0);

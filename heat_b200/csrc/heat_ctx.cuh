@@ -63,6 +63,7 @@ int eval_topk(Ctx *c, uint32_t k, const int64_t *train_indptr, const int32_t *tr
               int32_t *topk_ids_host, float *topk_scores_host);
 int eval_metrics(Ctx *c, const int64_t *train_indptr, const int32_t *train_items,
                  const int64_t *test_indptr, const int32_t *test_items, double out[6], double sums[7]);
+void eval_free(Ctx *c);
 // comm.cu
 int comm_unique_id(uint8_t out[128]);
 int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128]);
