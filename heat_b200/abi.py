@@ -28,7 +28,7 @@ SYMBOLS = [
     "heat_zero_grad", "heat_get_grads", "heat_set_lr", "heat_get_lr", "heat_get_epoch", "heat_set_epoch",
     "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
-    "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval",
+    "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
     "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free",
 ]
 
@@ -43,7 +43,7 @@ class HeatConfig(C.Structure):
         ("seed", C.c_uint64), ("sample_offset", C.c_uint64),
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
         ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
-        ("reserved1", C.c_uint32), ("max_blocks", C.c_uint32),
+        ("sync_average", C.c_uint32), ("max_blocks", C.c_uint32),
     ]
 
 
@@ -90,6 +90,7 @@ def lib():
         L.heat_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, _u8p]
         L.heat_comm_sync_items.argtypes = [C.c_void_p]
         L.heat_set_sync_interval.argtypes = [C.c_void_p, C.c_uint64]
+        L.heat_comm_allreduce_f64.argtypes = [C.c_void_p, _f64p, C.c_int]
         L.heat_probe_l2_bandwidth.argtypes = [C.c_int, C.c_uint64, C.c_int, _f64p]
         L.heat_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
         L.heat_host_free.argtypes = [C.c_void_p]
@@ -142,7 +143,7 @@ class Context:
 
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
-                 warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
+                 warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
                  device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
@@ -151,7 +152,8 @@ class Context:
                          milestones=_ptr(self._ms, _u64p), n_milestones=self._ms.size, seed=seed,
                          sample_offset=sample_offset, chunk=chunk, deterministic=int(bool(deterministic)),
                          w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
-                         max_blocks=max_blocks, update_mode=update_mode)
+                         max_blocks=max_blocks, update_mode=update_mode,
+                         sync_average=sync_average)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0
@@ -281,6 +283,11 @@ class Context:
 
     def comm_sync_items(self):
         _ck(lib().heat_comm_sync_items(self._h))
+
+    def allreduce_f64(self, vals):
+        v = np.ascontiguousarray(vals, np.float64).copy()
+        _ck(lib().heat_comm_allreduce_f64(self._h, _ptr(v, _f64p), v.size))
+        return v
 
     def set_sync_interval(self, samples):
         _ck(lib().heat_set_sync_interval(self._h, samples))

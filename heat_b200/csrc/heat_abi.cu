@@ -235,9 +235,17 @@ int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
     HEAT_CUDA(cudaEventRecord(c->ev_e0, c->stream));
     double total = 0.0;
     float ms_total = 0.f;
-    const uint64_t step = (c->world > 1 && c->sync_interval) ? c->sync_interval : N;
-    for (uint64_t b = 0; b < N; b += step) {
-        const uint64_t e = std::min(N, b + step);
+    // Multi-GPU: every rank runs the same number of segments (a collective follows each one), so
+    // the count comes from the largest shard; a rank's segment i is its own [N*i/nseg, N*(i+1)/nseg).
+    uint64_t nseg = 1;
+    if (c->world > 1 && c->sync_interval) {
+        uint64_t nmax = N;
+        int rc = comm_max_u64(c, &nmax);
+        if (rc) return rc;
+        nseg = std::max<uint64_t>(1, (nmax + c->sync_interval - 1) / c->sync_interval);
+    }
+    for (uint64_t i = 0; i < nseg; ++i) {
+        const uint64_t b = (uint64_t)((unsigned __int128)N * i / nseg), e = (uint64_t)((unsigned __int128)N * (i + 1) / nseg);
         double part = 0.0;
         int rc = launch_train(c, b, e, &part, nullptr);
         if (rc) return rc;
@@ -251,7 +259,10 @@ int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
     HEAT_CUDA(cudaStreamSynchronize(c->stream));
     cudaEventElapsedTime(&c->last_epoch_ms, c->ev_e0, c->ev_e1);
     c->epoch += 1;                                      // engine.cpp:378
-    if (mean_loss) *mean_loss = N ? total / (double)N : 0.0;
+    double samples = (double)N;
+    rc = comm_reduce_loss(c, &total, &samples);         // engine.cpp:380-383
+    if (rc) return rc;
+    if (mean_loss) *mean_loss = samples > 0 ? total / samples : 0.0;
     return 0;
 }
 
@@ -364,6 +375,13 @@ int heat_comm_sync_items(heat_ctx *ctx)
     if (!c) return fail("heat_comm_sync_items: null context");
     HEAT_CUDA(cudaSetDevice(c->device));
     return comm_sync_items(c);
+}
+int heat_comm_allreduce_f64(heat_ctx *ctx, double *vals, int n)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !vals || n < 0) return fail("heat_comm_allreduce_f64: bad argument");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return comm_allreduce_f64(c, vals, n);
 }
 int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples)
 {

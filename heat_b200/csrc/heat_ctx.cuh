@@ -37,8 +37,9 @@ struct Ctx {
     // multi-GPU
     int rank = 0, world = 1;
     void *nccl_comm = nullptr;
-    float *item_base = nullptr, *w0_base = nullptr;
-    uint64_t sync_interval = 0;
+    float *item_base = nullptr, *w0_base = nullptr, *delta = nullptr;
+    double *loss_pair = nullptr;
+    uint64_t sync_interval = 0, syncs = 0;
 
     // evaluation scratch (lazily sized)
     void *eval_scratch = nullptr;
@@ -68,6 +69,9 @@ void eval_free(Ctx *c);
 int comm_unique_id(uint8_t out[128]);
 int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128]);
 int comm_sync_items(Ctx *c);
+int comm_reduce_loss(Ctx *c, double *loss_sum, double *samples);
+int comm_allreduce_f64(Ctx *c, double *vals, int n);
+int comm_max_u64(Ctx *c, uint64_t *v);
 void comm_destroy(Ctx *c);
 // probe.cu
 int probe_l2(int device, uint64_t bytes, int iters, double *gbps);

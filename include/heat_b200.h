@@ -58,7 +58,8 @@ typedef struct heat_config {
     uint32_t update_mode;       /* item-row write-back in the Hogwild grid: 0 store the stepped snapshot (the
                                    reference's sequence), 1 re-read the rows right before the step, 2 apply the
                                    step as L2 vector reductions (no lost updates). deterministic=1 forces 0 */
-    uint32_t reserved1;
+    uint32_t sync_average;      /* multi-GPU item/W0 reconciliation: 0 base += sum of rank deltas (default),
+                                   1 base += mean of rank deltas (the fork's averaging, engine.cpp:371-373) */
     uint32_t max_blocks;        /* 0 = one grid over all SMs; else cap on thread blocks (bounds Hogwild concurrency) */
 } heat_config;
 
@@ -149,6 +150,9 @@ int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[1
  * the W0 delta since the last sync; every rank ends with base + sum of deltas. */
 int heat_comm_sync_items(heat_ctx *ctx);
 int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);   /* 0 = once per epoch */
+/* replaces: MPI_Allreduce of loss / iteration count (engine.cpp:380-383) for caller-side sums, e.g. the
+ * seven metric sums of heat_eval_metrics on user-sharded evaluation: vals[n] (n <= 16) summed over ranks. */
+int heat_comm_allreduce_f64(heat_ctx *ctx, double *vals, int n);
 
 /* ---- measurement helpers ------------------------------------------------------------ */
 /* L2-resident row gather/scatter micro-benchmark used as the L2 roofline denominator:
