@@ -64,13 +64,32 @@ __device__ __forceinline__ void red4(float *p, const float4 &v)
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
-__device__ __forceinline__ float4 operator+(const float4 &a, const float4 &b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
-__device__ __forceinline__ float4 operator-(const float4 &a, const float4 &b) { return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
-__device__ __forceinline__ float4 operator*(float s, const float4 &a) { return make_float4(s * a.x, s * a.y, s * a.z, s * a.w); }
-__device__ __forceinline__ float dot4(const float4 &a, const float4 &b) { return fmaf(a.w, b.w, fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x))); }
+// float4 arithmetic on Blackwell's packed fp32x2 pipe (FADD2 / FMUL2 / FFMA2: two IEEE fp32 results per
+// issued instruction, same rounding as the scalar forms), so a row slice costs 2 issue slots, not 4.
+__device__ __forceinline__ float2 lo2(const float4 &a) { return make_float2(a.x, a.y); }
+__device__ __forceinline__ float2 hi2(const float4 &a) { return make_float2(a.z, a.w); }
+__device__ __forceinline__ float4 cat4(const float2 &l, const float2 &h) { return make_float4(l.x, l.y, h.x, h.y); }
+__device__ __forceinline__ float4 operator+(const float4 &a, const float4 &b) { return cat4(__fadd2_rn(lo2(a), lo2(b)), __fadd2_rn(hi2(a), hi2(b))); }
+__device__ __forceinline__ float4 operator-(const float4 &a, const float4 &b)
+{
+    const float2 m1 = make_float2(-1.f, -1.f);      // a - b = fma(b, -1, a): exact product, one rounding
+    return cat4(__ffma2_rn(lo2(b), m1, lo2(a)), __ffma2_rn(hi2(b), m1, hi2(a)));
+}
+__device__ __forceinline__ float4 operator*(float s, const float4 &a)
+{
+    const float2 s2 = make_float2(s, s);
+    return cat4(__fmul2_rn(s2, lo2(a)), __fmul2_rn(s2, hi2(a)));
+}
+// x*x' + y*y' + z*z' + w*w' as (x*x' + z*z') + (y*y' + w*w')
+__device__ __forceinline__ float dot4(const float4 &a, const float4 &b)
+{
+    const float2 t = __ffma2_rn(hi2(a), hi2(b), __fmul2_rn(lo2(a), lo2(b)));
+    return t.x + t.y;
+}
 __device__ __forceinline__ void fma4(float4 &acc, float s, const float4 &a)
 {
-    acc.x = fmaf(s, a.x, acc.x); acc.y = fmaf(s, a.y, acc.y); acc.z = fmaf(s, a.z, acc.z); acc.w = fmaf(s, a.w, acc.w);
+    const float2 s2 = make_float2(s, s);
+    acc = cat4(__ffma2_rn(s2, lo2(a), lo2(acc)), __ffma2_rn(s2, hi2(a), hi2(acc)));
 }
 __device__ __forceinline__ float clampf(float g, float c) { return fmaxf(fminf(g, c), -c); }   // optimizer.cpp:17-22
 __device__ __forceinline__ float4 clamp4(const float4 &g, float c) { return make_float4(clampf(g.x, c), clampf(g.y, c), clampf(g.z, c), clampf(g.w, c)); }
@@ -172,7 +191,7 @@ __device__ __forceinline__ void w0_flush(const float *ring, float *W0s, float *w
 
 // D: embedding dim (32/64/128).  NJ: negative rows held per row group (K <= NJ * 32/(D/4)).
 // WARPS: warps per block.  PRELOAD_G: negative grad rows loaded up front with the weights.
-template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD>
+template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD, bool CACHE>
 __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams P)
 {
     constexpr int VL = D / 4;        // lanes per row
@@ -200,6 +219,16 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
     double loss_acc = 0.0;
     const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
 
+    // CACHE: state carried across the consecutive samples of one user (a "run").  The history column
+    // sums are gathered once per run and then patched with the exact change of every history row this
+    // warp itself rewrites; the user's weight and grad rows stay in registers.  In file order with one
+    // warp this is the reference's arithmetic up to fp32 re-association of the column sums (the run is
+    // re-gathered every REGATHER samples to bound that drift); under Hogwild, rows changed by OTHER
+    // warps during the run are seen at the next gather instead of at the next sample.
+    constexpr int REGATHER = 64;
+    int cur_u = -1, H = 0, age = 0;
+    float4 acc = f4zero(), u_keep = f4zero(), gu_keep = f4zero();
+
     for (;;) {
         unsigned long long c = 0;
         if (lane == 0) c = atomicAdd(P.chunk_counter, 1ULL);
@@ -220,9 +249,15 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             const bool dup = __any_sync(FULL, (same & (same - 1)) != 0);
 
             // ---- issue the row gathers
-            const float4 uw = ldcg4(P.user_w + (size_t)u * D + 4 * sl);
+            const bool fresh = !CACHE || u != cur_u || age >= REGATHER;      // warp-uniform
+            float4 uw, gu_old;
+            if (fresh) {
+                uw = ldcg4(P.user_w + (size_t)u * D + 4 * sl);
+                gu_old = ldcg4(P.user_g + (size_t)u * D + 4 * sl);
+            } else {
+                uw = u_keep; gu_old = gu_keep;
+            }
             float4 pw = ldcg4(P.item_w + (size_t)p * D + 4 * sl);
-            const float4 gu_old = ldcg4(P.user_g + (size_t)u * D + 4 * sl);
             const float4 gp_old = ldcg4(P.item_g + (size_t)p * D + 4 * sl);
             int nid[NJ];
             float4 nw[NJ];
@@ -237,23 +272,48 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             }
 
             // ---- history aggregation (behavior_aggregators.cpp:60-105)
-            const int H = __ldg(P.masks + u);
-            int hid[4];
-            load_history_ids(P, u, lane, hid);
-            float4 acc = f4zero();
-            for (int h0 = 0; h0 < H; h0 += R * UNR) {
-                const int hq = pick4(hid, h0 >> 5);
-                float4 t[UNR];
+            if (fresh) {
+                H = __ldg(P.masks + u);
+                int hid[4];
+                load_history_ids(P, u, lane, hid);
+                acc = f4zero();
+                for (int h0 = 0; h0 < H; h0 += R * UNR) {
+                    const int hq = pick4(hid, h0 >> 5);
+                    float4 t[UNR];
 #pragma unroll
-                for (int i = 0; i < UNR; ++i) {
-                    const int h = h0 + i * R + g;
-                    const int id = __shfl_sync(FULL, hq, h & 31);
-                    t[i] = (h < H) ? ldcg4(P.item_w + (size_t)id * D + 4 * sl) : f4zero();
+                    for (int i = 0; i < UNR; ++i) {
+                        const int h = h0 + i * R + g;
+                        const int id = __shfl_sync(FULL, hq, h & 31);
+                        t[i] = (h < H) ? ldcg4(P.item_w + (size_t)id * D + 4 * sl) : f4zero();
+                    }
+#pragma unroll
+                    for (int i = 0; i < UNR; ++i) acc = acc + t[i];
                 }
-#pragma unroll
-                for (int i = 0; i < UNR; ++i) acc = acc + t[i];
+                acc = cross_sum4<VL>(acc);
+                cur_u = u; age = 0;
             }
-            acc = cross_sum4<VL>(acc);
+            // CACHE: which of the item rows this sample rewrites are in the user's history list?
+            // (p: with multiplicity, its change is patched into `acc`; a negative: rare, re-gather)
+            int pmult = 0;
+            bool regather = false;
+            if (CACHE) {
+                constexpr int NPASS = (NJ * R + 15) / 16;
+                const int *hrow = P.his + (size_t)u * P.max_his;
+                bool nhit = false;
+                for (int c0 = 0; c0 < H; c0 += 16) {
+                    const int hi = c0 + lane - 16;
+                    const int hv = (lane >= 16 && hi < H) ? __ldg(hrow + hi) : (-64 - lane);
+                    pmult += __popc(__ballot_sync(FULL, hv == p));
+#pragma unroll
+                    for (int ps = 0; ps < NPASS; ++ps) {
+                        const int nv = __shfl_sync(FULL, negid, (ps * 16 + (lane & 15)) & 31);
+                        const unsigned mm = __match_any_sync(FULL, lane < 16 ? nv : hv);
+                        nhit |= (lane < 16) && (mm >> 16) != 0;
+                    }
+                }
+                const bool pin = __any_sync(FULL, negid == p);
+                regather = __any_sync(FULL, nhit) || (pmult != 0 && (dup || pin));
+            }
             const float rH = (float)(1.0 / (double)H);     // behavior_aggregators.cpp:63
             const float4 mean = rH * acc;
             float *ms = ring + (iter & 31) * 2 * D;
@@ -408,6 +468,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             gu = clamp4(gu, P.clip);
             fma4(ua, -P.lr, gu);
             float *prow = P.item_w + (size_t)p * D + 4 * sl, *pgrow = P.item_g + (size_t)p * D + 4 * sl;
+            static_assert(!(CACHE && UPD == UPD_FRESH), "the run cache needs the positive row's own delta");
             if (UPD == UPD_STORE) {
                 gp = clamp4(gp, P.clip);
                 fma4(pw, -P.lr, gp);
@@ -429,6 +490,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             }
             if (R == 1 || g == 0) stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
             if (R == 1 || g == 1) stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
+            if (CACHE) {
+                u_keep = ua; gu_keep = gu;
+                age = regather ? REGATHER : age + 1;
+                if (pmult != 0 && !regather) fma4(acc, -P.lr * (float)pmult, gp);     // I[p] moved by -lr*gp
+            }
             if (P.loss_out && lane == 0) P.loss_out[s - P.begin] = loss;
             loss_acc += (double)loss;
         }

@@ -6,10 +6,10 @@ namespace heat {
 
 namespace {
 
-template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD = UPD_STORE>
+template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD = UPD_STORE, bool CACHE = false>
 int launch_one(Ctx *c, const TrainParams &P, int blocks)
 {
-    auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G, UPD>;
+    auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G, UPD, CACHE>;
     const size_t smem = (size_t)(D * D + WARPS * 32 * 2 * D) * sizeof(float);
     HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
@@ -30,31 +30,36 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic)
     int blocks = deterministic ? 1 : c->num_sms * bps;
     if (c->cfg.max_blocks && blocks > (int)c->cfg.max_blocks) blocks = (int)c->cfg.max_blocks;
     const int upd = deterministic ? (int)UPD_STORE : P.upd;
+    const bool cache = c->cfg.history_mode != 1;          // 0 default: run cache; 1: re-gather every sample
 #define HEAT_LAUNCH(D_, NJ_, W_, PG_) return launch_one<D_, NJ_, W_, PG_>(c, P, blocks)
 // Hogwild grid: the three item-row update modes of train_kernel.cuh
 #define HEAT_LAUNCH_UPD(D_, NJ_, W_, PG_)                                                   \
     do {                                                                                    \
-        if (upd == UPD_ATOMIC) return launch_one<D_, NJ_, W_, PG_, UPD_ATOMIC>(c, P, blocks); \
         if (upd == UPD_FRESH) return launch_one<D_, NJ_, W_, false, UPD_FRESH>(c, P, blocks); \
+        if (cache) {                                                                        \
+            if (upd == UPD_ATOMIC) return launch_one<D_, NJ_, W_, PG_, UPD_ATOMIC, true>(c, P, blocks); \
+            return launch_one<D_, NJ_, W_, PG_, UPD_STORE, true>(c, P, blocks);             \
+        }                                                                                   \
+        if (upd == UPD_ATOMIC) return launch_one<D_, NJ_, W_, PG_, UPD_ATOMIC>(c, P, blocks); \
         return launch_one<D_, NJ_, W_, PG_, UPD_STORE>(c, P, blocks);                       \
     } while (0)
     if (D == 64 && K <= 16) {
-        if (deterministic) HEAT_LAUNCH(64, 8, 1, true);
+        if (deterministic) { if (cache) return launch_one<64, 8, 1, true, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(64, 8, 1, true); }
         if (warps == 0) warps = 12;
         if (warps <= 4) HEAT_LAUNCH_UPD(64, 8, 4, true);
         if (warps <= 8) HEAT_LAUNCH_UPD(64, 8, 8, true);
         HEAT_LAUNCH_UPD(64, 8, 12, true);
     }
     if (D == 64 && K <= 32) {
-        if (deterministic) HEAT_LAUNCH(64, 16, 1, false);
+        if (deterministic) { if (cache) return launch_one<64, 16, 1, false, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(64, 16, 1, false); }
         HEAT_LAUNCH_UPD(64, 16, 8, false);
     }
     if (D == 128 && K <= 16) {
-        if (deterministic) HEAT_LAUNCH(128, 16, 1, false);
+        if (deterministic) { if (cache) return launch_one<128, 16, 1, false, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(128, 16, 1, false); }
         HEAT_LAUNCH_UPD(128, 16, 4, false);
     }
     if (D == 32 && K <= 32) {
-        if (deterministic) HEAT_LAUNCH(32, 8, 1, true);
+        if (deterministic) { if (cache) return launch_one<32, 8, 1, true, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(32, 8, 1, true); }
         HEAT_LAUNCH_UPD(32, 8, 8, true);
     }
 #undef HEAT_LAUNCH_UPD

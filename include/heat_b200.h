@@ -60,6 +60,9 @@ typedef struct heat_config {
                                    step as L2 vector reductions (no lost updates). deterministic=1 forces 0 */
     uint32_t sync_average;      /* multi-GPU item/W0 reconciliation: 0 base += sum of rank deltas (default),
                                    1 base += mean of rank deltas (the fork's averaging, engine.cpp:371-373) */
+    uint32_t history_mode;      /* 0 default: the history column sums are gathered once per run of a user's
+                                   consecutive samples and patched with the exact change of the rows the warp
+                                   rewrites; 1: re-gathered for every sample (the reference's literal sequence) */
     uint32_t max_blocks;        /* 0 = one grid over all SMs; else cap on thread blocks (bounds Hogwild concurrency) */
 } heat_config;
 
