@@ -43,7 +43,7 @@ class HeatConfig(C.Structure):
         ("seed", C.c_uint64), ("sample_offset", C.c_uint64),
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
         ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
-        ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("max_blocks", C.c_uint32),
+        ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("engine", C.c_uint32), ("max_blocks", C.c_uint32),
     ]
 
 
@@ -143,7 +143,7 @@ class Context:
 
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
-                 warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, history_mode=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
+                 warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, history_mode=0, engine=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
                  device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
@@ -153,7 +153,7 @@ class Context:
                          sample_offset=sample_offset, chunk=chunk, deterministic=int(bool(deterministic)),
                          w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
                          max_blocks=max_blocks, update_mode=update_mode,
-                         sync_average=sync_average, history_mode=history_mode)
+                         sync_average=sync_average, history_mode=history_mode, engine=engine)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0

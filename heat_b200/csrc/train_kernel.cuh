@@ -41,6 +41,7 @@ struct TrainParams {
     unsigned epoch;
     int max_his, num_items, K, chunk, drop_w0_tail;
     int upd;                 // item-row update mode, see UPD_* below
+    int no_cache;            // 1: gather the history rows for every sample (history_mode 1)
     float lr, lr_w0, clip;
 };
 
@@ -95,10 +96,10 @@ __device__ __forceinline__ float clampf(float g, float c) { return fmaxf(fminf(g
 __device__ __forceinline__ float4 clamp4(const float4 &g, float c) { return make_float4(clampf(g.x, c), clampf(g.y, c), clampf(g.z, c), clampf(g.w, c)); }
 
 // sum over the VL lanes that hold one row (result in every lane of the group)
-template <int VL> __device__ __forceinline__ float group_sum(float v)
+template <int VL> __device__ __forceinline__ float group_sum(float v, unsigned mask = FULL)
 {
 #pragma unroll
-    for (int o = VL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    for (int o = VL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
     return v;
 }
 // sum over the 32/VL row groups of the warp

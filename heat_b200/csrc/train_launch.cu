@@ -1,6 +1,7 @@
 // heat_b200/csrc/train_launch.cu -- instantiates and launches the fused training kernel.
 #include "heat_ctx.cuh"
 #include "train_kernel.cuh"
+#include "train_kernel_cta.cuh"
 
 namespace heat {
 
@@ -18,6 +19,38 @@ int launch_one(Ctx *c, const TrainParams &P, int blocks)
     HEAT_CUDA(cudaEventRecord(c->ev1, c->stream));
     c->launches += 1;
     return 0;
+}
+
+template <int D, int NPS>
+int launch_cta(Ctx *c, const TrainParams &P, int blocks)
+{
+    using C = CtaCfg<D, NPS>;
+    auto kern = train_cta_kernel<D, NPS>;
+    const size_t smem = (size_t)C::FLOATS * sizeof(float);
+    HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
+    kern<<<blocks, C::NT, smem, c->stream>>>(P);
+    HEAT_CUDA(cudaGetLastError());
+    HEAT_CUDA(cudaEventRecord(c->ev1, c->stream));
+    c->launches += 1;
+    return 0;
+}
+
+// CTA-per-sample engine (train_kernel_cta.cuh): returns -1 when (D, K) is outside what it covers.
+int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
+{
+    const int D = (int)c->cfg.emb_dim, K = P.K;
+    const int bps = c->cfg.blocks_per_sm ? (int)c->cfg.blocks_per_sm : 1;
+    int blocks = deterministic ? 1 : c->num_sms * bps;
+    if (c->cfg.max_blocks && blocks > (int)c->cfg.max_blocks) blocks = (int)c->cfg.max_blocks;
+    if (D == 64 && K <= 16) return launch_cta<64, 1>(c, P, blocks);
+    if (D == 64 && K <= 32) return launch_cta<64, 2>(c, P, blocks);
+    if (D == 64 && K <= 64) return launch_cta<64, 4>(c, P, blocks);
+    if (D == 128 && K <= 16) return launch_cta<128, 1>(c, P, blocks);
+    if (D == 128 && K <= 64) return launch_cta<128, 4>(c, P, blocks);
+    if (D == 32 && K <= 16) return launch_cta<32, 1>(c, P, blocks);
+    if (D == 32 && K <= 32) return launch_cta<32, 2>(c, P, blocks);
+    return -1;
 }
 
 // Pick the instantiation for (D, K, warps).  K must fit the register-resident path:
@@ -97,7 +130,11 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     P.upd = (int)c->cfg.update_mode;
     P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
 
-    int rc = dispatch(c, P, c->cfg.deterministic != 0);
+    P.no_cache = c->cfg.history_mode == 1;
+    int rc = -1;
+    if (c->cfg.engine != 1) rc = dispatch_cta(c, P, c->cfg.deterministic != 0);      // 0 auto, 2 forced
+    if (rc == -1 && c->cfg.engine == 2) rc = fail("engine 2 (CTA per sample) does not cover this (emb_dim, num_negs)");
+    if (rc == -1) rc = dispatch(c, P, c->cfg.deterministic != 0);
     if (rc == 0) {
         double loss = 0.0;
         cudaError_t e = cudaMemcpyAsync(&loss, c->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);

@@ -63,6 +63,9 @@ typedef struct heat_config {
     uint32_t history_mode;      /* 0 default: the history column sums are gathered once per run of a user's
                                    consecutive samples and patched with the exact change of the rows the warp
                                    rewrites; 1: re-gathered for every sample (the reference's literal sequence) */
+    uint32_t engine;            /* 0 auto; 1 warp-per-sample kernel (train_kernel.cuh: highest throughput, thousands of
+                                   samples in flight); 2 CTA-per-sample kernel (train_kernel_cta.cuh: lowest latency per
+                                   sample, one sample in flight per thread block -- the default where it applies) */
     uint32_t max_blocks;        /* 0 = one grid over all SMs; else cap on thread blocks (bounds Hogwild concurrency) */
 } heat_config;
 
