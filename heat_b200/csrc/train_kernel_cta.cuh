@@ -18,7 +18,8 @@
 //
 // Per sample: issue every row load, overlap the L2 round trip with mean.W0 and the user aggregation,
 // then dots -> [barrier] -> softmax (recomputed per slot from 2K+3 shared scalars) -> row updates ->
-// [barrier] -> user step -> [barrier].  Five block barriers, one L2 round trip on the critical path.
+// [barrier]; the user step of a sample overlaps the next sample's loads.  Three block barriers, one L2
+// round trip on the critical path.
 // Same arithmetic as train_kernel.cuh (reference: models/matrix_factorization.cpp:15-181,
 // behavior_aggregators/behavior_aggregators.cpp:51-153, optimizers/sgd.cpp:14-26); with one CTA the
 // samples are applied strictly in file order (deterministic mode).
@@ -28,7 +29,7 @@
 namespace heat {
 
 struct CtaMeta {            // one sample, prepared by the control warp
-    int u, p, fresh, dup, H, done;
+    int u, p, fresh, dup, H, done, pmult, regather;
     long long s;
     int negid[64];
 };
@@ -48,15 +49,23 @@ template <int D, int NPS> struct CtaCfg {
     static constexpr int OFF_MEAN = OFF_W0 + D * D;          // [2][D]
     static constexpr int OFF_ACC = OFF_MEAN + 2 * D;         // [D] history column sums
     static constexpr int OFF_FPART = OFF_ACC + D;            // [4][D]
-    static constexpr int OFF_UA = OFF_FPART + 4 * D;         // [D]
+    static constexpr int OFF_UA = OFF_FPART + 4 * D;         // [D] the user's stored row (input of the aggregation)
     static constexpr int OFF_PW = OFF_UA + D;                // [D]
-    static constexpr int OFF_GP = OFF_PW + D;                // [D] clipped positive grad row
+    static constexpr int OFF_GP = OFF_PW + D;                // [D] (spare)
     static constexpr int OFF_GU06 = OFF_GP + D;              // [D] 0.6 * user grad (W0 outer product)
-    static constexpr int OFF_PART = OFF_GU06 + D;            // [NSLOT][D] partial sums (history gather / user grad)
-    static constexpr int OFF_SC = OFF_PART + NSLOT * D;      // un[KMAX], nn[KMAX], uu, pp, up
+    static constexpr int OFF_PART = OFF_GU06 + D;            // [16][D] user-grad partial sums of the negative slots
+    static constexpr int OFF_HPART = OFF_PART + 16 * D;      // [NSLOT][D] history-gather partial sums
+    static constexpr int OFF_SC = OFF_HPART + NSLOT * D;     // un[KMAX], nn[KMAX], pp, up
     static constexpr int OFF_META = OFF_SC + 2 * KMAX + 8;   // 2 x CtaMeta
     static constexpr int FLOATS = OFF_META + 2 * (int)(sizeof(CtaMeta) / 4) + 8;
 };
+
+// Barrier over the row threads only (named barrier 1): the control warp is not on the critical path of
+// the sample being processed, it meets the row threads at the two full barriers [B] and [C].
+template <int NROW> __device__ __forceinline__ void row_bar(bool is_ctrl)
+{
+    if (!is_ctrl) asm volatile("bar.sync 1, %0;" ::"n"(NROW) : "memory");
+}
 
 template <int VL> __device__ __forceinline__ float group_max(float v, unsigned mask)
 {
@@ -132,10 +141,11 @@ __device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, in
     }
     regather = __any_sync(FULL, nhit) || (pmult != 0 && dup);
     age += 1;
-    if (lane == 0) { m->u = u; m->p = p; m->fresh = fresh; m->dup = dup; m->H = H; m->done = 0; m->s = s; }
+    if (lane == 0) { m->u = u; m->p = p; m->fresh = fresh; m->dup = dup; m->H = H; m->done = 0; m->s = s; m->pmult = pmult; m->regather = regather; }
     (void)KMAX;
     s += 1;
 }
+
 
 template <int D, int NPS>
 __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const TrainParams P)
@@ -144,8 +154,9 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     constexpr int LPR = C::LPR, NSLOT = C::NSLOT, KMAX = C::KMAX, IQ = C::IQ;
     extern __shared__ __align__(16) float smem[];
     float *W0s = smem + C::OFF_W0, *meanb = smem + C::OFF_MEAN, *accs = smem + C::OFF_ACC, *fpart = smem + C::OFF_FPART;
-    float *ua_s = smem + C::OFF_UA, *pw_s = smem + C::OFF_PW, *gp_s = smem + C::OFF_GP, *gu06_s = smem + C::OFF_GU06;
-    float *part = smem + C::OFF_PART, *sc_un = smem + C::OFF_SC, *sc_nn = sc_un + KMAX, *sc3 = sc_nn + KMAX;
+    float *urow_s = smem + C::OFF_UA, *pw_s = smem + C::OFF_PW, *gu06_s = smem + C::OFF_GU06;
+    float *part = smem + C::OFF_PART, *hpart = smem + C::OFF_HPART;
+    float *sc_un = smem + C::OFF_SC, *sc_nn = sc_un + KMAX, *sc3 = sc_nn + KMAX;
     CtaMeta *meta = reinterpret_cast<CtaMeta *>(smem + C::OFF_META);
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -157,6 +168,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     const int gj = tid % D, giq = tid / D;                   // GEMV column / row block (valid when is_gemv)
     // lanes of this thread's row slot: slots of one warp take different branches, so every shuffle names its own group
     const unsigned gmask = LPR >= 32 ? FULL : (((1u << (LPR & 31)) - 1u) << ((lane / LPR) * LPR));
+    const int gbase = (lane / LPR) * LPR;
 
     for (int i = tid * 4; i < D * D; i += C::NT * 4) *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
 
@@ -166,19 +178,39 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
     const bool no_cache = P.no_cache != 0;
 
-    // control-warp state
-    long long c_s = 0, c_end = 0;
-    int c_u = -1, c_H = 0, c_age = 0, c_pmult = 0, pmult_cur = 0;
-    bool c_regather = false, regather_cur = false;
-    // row-thread state
-    float4 u_keep = f4zero(), gu_keep = f4zero();
-    float w0acc[IQ];
+    long long c_s = 0, c_end = 0;                            // control-warp state
+    int c_u = -1, c_H = 0, c_age = 0, c_pmult = 0;
+    bool c_regather = false;
+    float4 u_keep = f4zero(), gu_keep = f4zero();            // user slot: the run's user row / grad row
+    float w0acc[IQ];                                         // GEMV threads: W0 gradient accumulator
 #pragma unroll
     for (int i = 0; i < IQ; ++i) w0acc[i] = 0.f;
     unsigned iter = 0;
     double loss_acc = 0.0;
     bool have_tail = false;                                  // W0 outer product of the previous sample pending
     int cur = 0;
+
+    // W0 gradient of the sample whose mean is in `pm_all` (behavior_aggregators.cpp:131-146)
+    auto w0_tail = [&](const float *pm_all, bool flush, bool refresh_smem) {
+        const float *pm = pm_all + giq * IQ;
+        const float gq = gu06_s[gj];
+#pragma unroll
+        for (int i4 = 0; i4 < IQ; i4 += 4) {
+            const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
+            w0acc[i4 + 0] = fmaf(m4.x, gq, w0acc[i4 + 0]); w0acc[i4 + 1] = fmaf(m4.y, gq, w0acc[i4 + 1]);
+            w0acc[i4 + 2] = fmaf(m4.z, gq, w0acc[i4 + 2]); w0acc[i4 + 3] = fmaf(m4.w, gq, w0acc[i4 + 3]);
+        }
+        if (flush) {
+#pragma unroll
+            for (int i = 0; i < IQ; ++i) {
+                const int e = (giq * IQ + i) * D + gj;
+                const float delta = -(P.lr_w0 * (w0acc[i] / 32.0f));
+                const float old = atomicAdd(P.w0 + e, delta);
+                if (refresh_smem) W0s[e] = old + delta;
+                w0acc[i] = 0.f;
+            }
+        }
+    };
 
     if (is_ctrl) {
         if (lane == 0) meta[0].done = 0;
@@ -193,7 +225,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         const bool fresh = m->fresh != 0, dup = m->dup != 0;
         const float rH = (float)(1.0 / (double)H);          // behavior_aggregators.cpp:63
         float *mean = meanb + cur * D;
-        if (is_ctrl) { pmult_cur = c_pmult; regather_cur = c_regather; }
 
         // ---- issue the row loads of this sample
         int nid[NPS];
@@ -217,23 +248,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             } else {
                 rw = u_keep; rg = gu_keep;
             }
-        }
-        // ---- W0 gradient of the previous sample (registers), flush every 32 samples
-        if (have_tail && is_gemv) {
-            const float *pm = meanb + (cur ^ 1) * D + giq * IQ;
-            const float gq = gu06_s[gj];
-#pragma unroll
-            for (int i = 0; i < IQ; ++i) w0acc[i] = fmaf(pm[i], gq, w0acc[i]);          // behavior_aggregators.cpp:131-139
-            if ((iter & 31) == 0) {
-#pragma unroll
-                for (int i = 0; i < IQ; ++i) {
-                    const int e = (giq * IQ + i) * D + gj;
-                    const float delta = -(P.lr_w0 * (w0acc[i] / 32.0f));                   // :141-146
-                    const float old = atomicAdd(P.w0 + e, delta);
-                    W0s[e] = old + delta;
-                    w0acc[i] = 0.f;
-                }
-            }
+            *reinterpret_cast<float4 *>(urow_s + 4 * sl) = rw;
         }
         // ---- first sample of a run: gather the history rows (behavior_aggregators.cpp:96-105)
         if (fresh) {
@@ -241,48 +256,56 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 const int *hrow = P.his + (size_t)u * P.max_his;
                 float4 a4 = f4zero();
                 for (int h = slot; h < H; h += NSLOT) a4 = a4 + ldcg4(P.item_w + (size_t)__ldg(hrow + h) * D + 4 * sl);
-                *reinterpret_cast<float4 *>(part + slot * D + 4 * sl) = a4;
+                *reinterpret_cast<float4 *>(hpart + slot * D + 4 * sl) = a4;
             }
-            __syncthreads();
+            row_bar<C::CTRL0>(is_ctrl);
             if (tid < D) {
                 float a = 0.f;
 #pragma unroll
-                for (int q = 0; q < NSLOT; ++q) a += part[q * D + tid];
+                for (int q = 0; q < NSLOT; ++q) a += hpart[q * D + tid];
                 accs[tid] = a;
                 mean[tid] = a * rH;
             }
-            __syncthreads();
+            row_bar<C::CTRL0>(is_ctrl);
+        }
+        // ---- a W0 step is due (every 32 samples): it must land before this sample's mean.W0
+        const bool flush_due = have_tail && (iter & 31) == 0;
+        if (flush_due) {
+            row_bar<C::CTRL0>(is_ctrl);                       // the user slot has published 0.6*g_u of the previous sample
+            if (is_gemv) w0_tail(meanb + (cur ^ 1) * D, true, true);
         }
         // ---- f = mean . W0 as four partial GEMVs (behavior_aggregators.cpp:118)
         if (is_gemv) {
             const float *pm = mean + giq * IQ;
-            float f = 0.f;
+            float f0 = 0.f, f1 = 0.f, f2 = 0.f, f3 = 0.f;
 #pragma unroll
-            for (int i = 0; i < IQ; ++i) f = fmaf(pm[i], W0s[(giq * IQ + i) * D + gj], f);
-            fpart[giq * D + gj] = f;
+            for (int i4 = 0; i4 < IQ; i4 += 4) {
+                const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
+                const float *w = W0s + (giq * IQ + i4) * D + gj;
+                f0 = fmaf(m4.x, w[0], f0); f1 = fmaf(m4.y, w[D], f1); f2 = fmaf(m4.z, w[2 * D], f2); f3 = fmaf(m4.w, w[3 * D], f3);
+            }
+            fpart[giq * D + gj] = (f0 + f1) + (f2 + f3);
         }
-        // ---- control warp: prepare the next sample while the rows are in flight
+        // ---- control warp: prepare the next sample while this one is processed (meets the others at [B])
         if (is_ctrl) {
             if (lane == 0) meta[cur ^ 1].done = 0;
             cta_prepare<D, NPS>(P, &meta[cur ^ 1], lane, c_s, c_end, nchunks, c_u, c_H, c_age, c_regather, c_pmult, no_cache);
         }
-        __syncthreads();                                                              // [G1]
-        // ---- u <- gamma*u + (1-gamma)*f (:122); uu
+        row_bar<C::CTRL0>(is_ctrl);                                                   // [G1]
+        if (have_tail && !flush_due && is_gemv) w0_tail(meanb + (cur ^ 1) * D, false, false);
+        // ---- every row slot: u <- gamma*u + (1-gamma)*f (:122), uu
         float4 ua = f4zero();
-        if (is_usr) {
+        float uu = 0.f;
+        if (is_row) {
             const float4 f0 = *reinterpret_cast<const float4 *>(fpart + 4 * sl), f1 = *reinterpret_cast<const float4 *>(fpart + D + 4 * sl);
             const float4 f2 = *reinterpret_cast<const float4 *>(fpart + 2 * D + 4 * sl), f3 = *reinterpret_cast<const float4 *>(fpart + 3 * D + 4 * sl);
             const float4 f = (f0 + f1) + (f2 + f3);
-            ua = gamma * rw;
+            ua = gamma * *reinterpret_cast<const float4 *>(urow_s + 4 * sl);
             fma4(ua, omg, f);
-            *reinterpret_cast<float4 *>(ua_s + 4 * sl) = ua;
-            const float uu_ = group_sum<LPR>(dot4(ua, ua), gmask);
-            if (sl == 0) sc3[0] = uu_;
+            uu = group_sum<LPR>(dot4(ua, ua), gmask);
         }
-        __syncthreads();                                                              // [G2]
         // ---- dots (matrix_factorization.cpp:45-47, 82-85)
         if (is_neg) {
-            ua = *reinterpret_cast<const float4 *>(ua_s + 4 * sl);
 #pragma unroll
             for (int n = 0; n < NPS; ++n) {
                 const int k = slot + 16 * n;
@@ -290,45 +313,45 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 if (sl == 0 && k < K) { sc_un[k] = un_; sc_nn[k] = nn_; }
             }
         } else if (is_pos) {
-            ua = *reinterpret_cast<const float4 *>(ua_s + 4 * sl);
             const float pp_ = group_sum<LPR>(dot4(rw, rw), gmask), up_ = group_sum<LPR>(dot4(ua, rw), gmask);
             if (sl == 0) { sc3[1] = pp_; sc3[2] = up_; }
             *reinterpret_cast<float4 *>(pw_s + 4 * sl) = rw;
         }
-        __syncthreads();                                                              // [A]
+        row_bar<C::CTRL0>(is_ctrl);                                                   // [A]
         // ---- scores and softmax, recomputed by every row slot from the shared scalars
-        //      (matrix_factorization.cpp:55-61, 91-109)
-        float lgsum = 0.f, bsum = 0.f, m_ = 0.f, esum = 0.f, unorm = 0.f, unorm3 = 0.f, pnorm = 0.f, uu = 0.f, pp = 0.f, upd = 0.f;
+        //      (matrix_factorization.cpp:55-61, 91-109).  log(1 + sum_k exp(score_k)) is evaluated without
+        //      the reference's max shift: |score| <= 2/0.07, far inside fp32 range, same value to rounding.
+        float lgsum = 0.f, bsum = 0.f, esum = 0.f, unorm = 0.f, unorm3 = 0.f, pnorm = 0.f, pp = 0.f, upd = 0.f;
+        constexpr int SPL = (KMAX + LPR - 1) / LPR;
+        float k1[SPL], k2[SPL], k3[SPL];                       // per-k update coefficients, lane sl holds k = sl + LPR*q
         if (is_row) {
-            uu = sc3[0]; pp = sc3[1]; upd = sc3[2];
+            pp = sc3[1]; upd = sc3[2];
             unorm = sqrtf(fmaxf(uu, eps)); pnorm = sqrtf(fmaxf(pp, eps));
             unorm3 = unorm * unorm * unorm;
             const float cos_p = upd / (unorm * pnorm);
-            constexpr int SPL = (KMAX + LPR - 1) / LPR;
-            float scv[SPL], cb[SPL];
-            m_ = -INFINITY;
+            float ev[SPL], r3[SPL], rn3[SPL], unv[SPL], nnv[SPL];
 #pragma unroll
             for (int q = 0; q < SPL; ++q) {
                 const int k = sl + LPR * q;
-                scv[q] = -INFINITY; cb[q] = 0.f;
+                ev[q] = 0.f; r3[q] = 0.f; rn3[q] = 0.f; unv[q] = 0.f; nnv[q] = 0.f;
                 if (k < K) {
-                    const float nn_ = sc_nn[k], un_ = sc_un[k];
-                    const float nnorm = sqrtf(nn_ < eps ? eps : nn_);
-                    scv[q] = (un_ / (unorm * nnorm) - cos_p) * score_mul;
-                    cb[q] = -(1.f / (unorm3 * nnorm)) * un_;
+                    nnv[q] = sc_nn[k]; unv[q] = sc_un[k];
+                    const float nnorm = sqrtf(nnv[q] < eps ? eps : nnv[q]);
+                    ev[q] = expf((unv[q] / (unorm * nnorm) - cos_p) * score_mul);
+                    r3[q] = 1.f / (unorm3 * nnorm);                        // :136
+                    rn3[q] = 1.f / (unorm * (nnorm * nnorm * nnorm));      // :137
                 }
-                m_ = fmaxf(m_, scv[q]);
+                esum += ev[q];
             }
-            m_ = group_max<LPR>(m_, gmask);
-#pragma unroll
-            for (int q = 0; q < SPL; ++q) { scv[q] = expf(scv[q] - m_); esum += scv[q]; }
-            esum = group_sum<LPR>(esum, gmask);
-            esum += expf(-m_);                                 // the implicit zero logit (:107)
+            esum = group_sum<LPR>(esum, gmask) + 1.0f;         // the implicit zero logit (:107)
             const float inv_esum = 1.f / esum;
 #pragma unroll
             for (int q = 0; q < SPL; ++q) {
-                const float lg = (scv[q] * inv_esum) * score_mul;   // :109
-                lgsum += lg; bsum = fmaf(lg, cb[q], bsum);
+                const float lg = (ev[q] * inv_esum) * score_mul;   // :109
+                lgsum += lg; bsum = fmaf(lg, -(r3[q] * unv[q]), bsum);
+                k1[q] = lg * rn3[q] * nnv[q];                  // lg*gn_n = k1*u + k2*N[k] (:139,:143)
+                k2[q] = -(lg * rn3[q]) * unv[q];
+                k3[q] = lg * r3[q] * uu;                       // the N[k] part of lg*gu_n (:138,:141)
             }
             lgsum = group_sum<LPR>(lgsum, gmask);
             bsum = group_sum<LPR>(bsum, gmask);
@@ -336,22 +359,20 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         // ---- negative rows: grads, clipped step, write-back (:127-150; sgd.cpp:14-26)
         if (is_neg) {
             float4 gpart = f4zero();
-            const float inv_esum = 1.f / esum;
             float c1[NPS], c2[NPS];
 #pragma unroll
             for (int n = 0; n < NPS; ++n) {
-                const int k = slot + 16 * n;
+                const int k = slot + 16 * n;                   // its coefficients live in lane k % LPR, entry k / LPR
+                float c3 = 0.f;
                 c1[n] = 0.f; c2[n] = 0.f;
-                if (k < K) {
-                    const float nn_ = sc_nn[k], un_ = sc_un[k];
-                    const float nnorm = sqrtf(nn_ < eps ? eps : nn_);
-                    const float cos_p = upd / (unorm * pnorm);
-                    const float sc = (un_ / (unorm * nnorm) - cos_p) * score_mul;
-                    const float lg = (expf(sc - m_) * inv_esum) * score_mul;
-                    const float r_u3_n = 1.f / (unorm3 * nnorm), r_u_n3 = 1.f / (unorm * (nnorm * nnorm * nnorm));
-                    fma4(gpart, lg * r_u3_n * uu, nw[n]);                    // the N[k] part of lg*(gu_n) (:138,:141)
-                    c1[n] = lg * r_u_n3 * nn_; c2[n] = -(lg * r_u_n3) * un_;  // lg*gn_n = c1*u + c2*N[k] (:139,:143)
+#pragma unroll
+                for (int q = 0; q < SPL; ++q) {
+                    const float a1 = __shfl_sync(gmask, k1[q], gbase + (k % LPR));
+                    const float a2 = __shfl_sync(gmask, k2[q], gbase + (k % LPR));
+                    const float a3 = __shfl_sync(gmask, k3[q], gbase + (k % LPR));
+                    if (q == k / LPR && k < K) { c1[n] = a1; c2[n] = a2; c3 = a3; }
                 }
+                fma4(gpart, c3, nw[n]);
             }
             *reinterpret_cast<float4 *>(part + slot * D + 4 * sl) = gpart;
             if (!dup) {
@@ -367,10 +388,9 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         stcg4(P.item_g + (size_t)nid[n] * D + 4 * sl, gk);   // :149
                     }
                 }
-            }
-            if (dup) {                                       // keep the coefficients for the replay below
+            } else {                                         // keep the coefficients for the replay below
 #pragma unroll
-                for (int n = 0; n < NPS; ++n) { gn[n] = make_float4(c1[n], c2[n], 0.f, 0.f); }
+                for (int n = 0; n < NPS; ++n) gn[n] = make_float4(c1[n], c2[n], 0.f, 0.f);
             }
         }
         if (dup) {
@@ -392,10 +412,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         }
                     }
                 }
-                __syncthreads();
+                row_bar<C::CTRL0>(is_ctrl);
             }
         }
-        // ---- positive row (:142, :169, :173-174)
+        // ---- positive row (:142, :169, :173-174); patch of the cached history sums
         if (is_pos) {
             const float r_u_p3 = 1.f / (unorm * (pnorm * pnorm * pnorm));
             float4 gp = rg;
@@ -405,15 +425,20 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             fma4(wp, -P.lr, gp);
             stcg4(P.item_w + (size_t)p * D + 4 * sl, wp);
             stcg4(P.item_g + (size_t)p * D + 4 * sl, gp);
-            *reinterpret_cast<float4 *>(gp_s + 4 * sl) = gp;
+            // I[p] moved by -lr*gp: carry that into the column sums and publish the mean of the run's next
+            // sample (if the next sample starts a new run or re-gathers, the gather overwrites both)
+            float4 a4 = *reinterpret_cast<const float4 *>(accs + 4 * sl);
+            fma4(a4, m->regather ? 0.f : -P.lr * (float)m->pmult, gp);
+            *reinterpret_cast<float4 *>(accs + 4 * sl) = a4;
+            *reinterpret_cast<float4 *>(meanb + (cur ^ 1) * D + 4 * sl) = rH * a4;
             if (sl == 0) {
-                const float loss = m_ + logf(esum);              // :108
+                const float loss = logf(esum);                   // :108
                 loss_acc += (double)loss;
                 if (P.loss_out) P.loss_out[m->s - P.begin] = loss;
             }
         }
         __syncthreads();                                                              // [B]
-        // ---- user row: grad, aggregator backward, step (:141, :152, :166, :171-172)
+        // ---- user row: grad, aggregator backward, step (:141, :152, :166, :171-172); overlaps the next sample's loads
         if (is_usr) {
             float4 gacc = f4zero();
 #pragma unroll
@@ -432,36 +457,13 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
             u_keep = ua; gu_keep = gu;
         }
-        // ---- control: patch the cached column sums with the positive row's own change, publish the next mean
-        if (is_ctrl) {
-            const CtaMeta *nx = &meta[cur ^ 1];
-            if (!nx->done && !nx->fresh) {
-                const float c = regather_cur ? 0.f : -P.lr * (float)pmult_cur;
-                const float rHn = (float)(1.0 / (double)nx->H);
-                for (int i = lane; i < D; i += 32) {
-                    const float a = fmaf(c, gp_s[i], accs[i]);
-                    accs[i] = a;
-                    meanb[(cur ^ 1) * D + i] = a * rHn;
-                }
-            }
-        }
         iter += 1;
         have_tail = true;
-        __syncthreads();                                                              // [C]
         cur ^= 1;
     }
     // ---- W0 gradient of the last sample and the leftover (< 32 samples) accumulators
-    if (have_tail && is_gemv) {
-        const float *pm = meanb + (cur ^ 1) * D + giq * IQ;
-        const float gq = gu06_s[gj];
-        const bool full = (iter & 31) == 0;
-#pragma unroll
-        for (int i = 0; i < IQ; ++i) w0acc[i] = fmaf(pm[i], gq, w0acc[i]);
-        if (full || !P.drop_w0_tail) {
-#pragma unroll
-            for (int i = 0; i < IQ; ++i) atomicAdd(P.w0 + (giq * IQ + i) * D + gj, -(P.lr_w0 * (w0acc[i] / 32.0f)));
-        }
-    }
+    __syncthreads();
+    if (have_tail && is_gemv) w0_tail(meanb + (cur ^ 1) * D, ((iter & 31) == 0) || !P.drop_w0_tail, false);
     if (is_pos && sl == 0 && loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
 }
 

@@ -37,9 +37,13 @@ ref_res, _ = evaluate(t)
 out["reference"] = {"losses": ref_losses, "sec_per_epoch": ref_s, "threads": o.max_threads(), **ref_res}
 print("reference", [round(x, 4) for x in ref_losses], {k: round(v, 4) for k, v in ref_res.items()}, f"{ref_s:.2f} s/epoch", flush=True)
 for mode in modes:
-    w, mb, upd = map(int, mode.split(":"))
     t = synth.init_tables(d.num_users, d.num_items, D)
-    ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, warps_per_block=w, max_blocks=mb, update_mode=upd)
+    if mode.startswith("cta"):            # cta:<max_blocks>:<blocks_per_sm>
+        _, mb, bps = mode.split(":")
+        ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=2, max_blocks=int(mb), blocks_per_sm=int(bps))
+    else:                                 # <warps>:<max_blocks>:<update_mode>  (warp-per-sample engine)
+        w, mb, upd = map(int, mode.split(":"))
+        ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=1, warps_per_block=w, max_blocks=mb, update_mode=upd)
     ctx.set_dataset(d.clicks, d.his_items, d.masks)
     ctx.bind_tables(*t)
     losses, ms = [], []
