@@ -43,7 +43,7 @@ def build_cuda(force=False, verbose=False):
     for src in CUDA_SOURCES:
         obj = os.path.join(HERE, "build", src + ".o")
         objs.append(obj)
-        cmd = ["nvcc", *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = ["nvcc", *NVCC_FLAGS, *os.environ.get("HEAT_NVCC_DEFS", "").split(), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((cmd, subprocess.Popen(cmd, cwd=CSRC)))

@@ -4,24 +4,26 @@
 // on how many samples are in flight: the loss / Recall of the reference at 1-128
 // threads is reproduced only while a few hundred samples at most are being processed concurrently.
 // Throughput at a FIXED number of samples in flight is (samples in flight) / (latency of one sample),
-// so this kernel spends a whole CTA on one sample to make that latency small (~1 us instead of the
-// ~5 us a single warp needs for the same arithmetic):
+// so this kernel spends a whole CTA on one sample to make that latency small:
 //
-//   slots 0..15   (D/4 lanes each)  own the negative rows k = slot, slot+16, ...   (NPS per slot)
-//   slot 16                          owns the positive row
-//   slot 17                          owns the user row (kept in registers across a user's run)
-//   threads 0..4D-1                  also compute mean.W0 (4 partial GEMVs) and own the D*D/(4D)
-//                                    = D/4 elements each of the W0 gradient accumulator (registers)
-//   control warp                     prepares the NEXT sample while the rows of this one are in
-//                                    flight: click, Philox negatives, duplicate detection, history
-//                                    membership; patches the cached history column sums
+//   neg slots 0..15 (D/4 lanes each, whole warps)  own the negative rows k = slot, slot+16, ... (NPS per slot)
+//   pos warp (D/4 lanes used)                       owns the positive row, the loss and the history-sum patch
+//   usr warp (D/4 lanes used)                       owns the user row (kept in registers across a user's run)
+//   threads 0..4D-1 (= the neg slots)               also compute mean.W0 as 4 partial GEMVs against a
+//                                                   REGISTER-resident slice of W0 (D <= 64) and own the
+//                                                   matching D/4 elements of the W0 gradient accumulator
+//   control warp                                    prepares the NEXT sample while this one is processed:
+//                                                   click, Philox negatives, duplicate detection, history
+//                                                   membership against the run's history ids (registers)
 //
-// Per sample: issue every row load, overlap the L2 round trip with mean.W0 and the user aggregation,
-// then dots -> [barrier] -> softmax (recomputed per slot from 2K+3 shared scalars) -> row updates ->
-// [barrier]; the user step of a sample overlaps the next sample's loads.  Three block barriers, one L2
-// round trip on the critical path.
+// Per sample, three block barriers and one L2 round trip on the critical path:
+//   issue all row loads | mean.W0  -[G1]-  u <- 0.4u + 0.6f, the 3 dots of every slot in one interleaved
+//   butterfly, E_k = exp(cos_k/T)  -[A]-  esum = 1 + exp(-cos_p/T)*sum_k E_k from 16 shared partials (no
+//   cross-slot shuffles), coefficients, clipped row steps, stores, W0 outer product of the PREVIOUS
+//   sample  -[B]-  user step (overlaps the next sample's loads and GEMV).
 // Same arithmetic as train_kernel.cuh (reference: models/matrix_factorization.cpp:15-181,
-// behavior_aggregators/behavior_aggregators.cpp:51-153, optimizers/sgd.cpp:14-26); with one CTA the
+// behavior_aggregators/behavior_aggregators.cpp:51-153, optimizers/sgd.cpp:14-26) up to fp32 rounding:
+// 1/sqrt via MUFU.RSQ (2 ulp), softmax as exp(a)*exp(-b) instead of exp(a-b-max).  With one CTA the
 // samples are applied strictly in file order (deterministic mode).
 #pragma once
 #include "train_kernel.cuh"
@@ -31,73 +33,106 @@ namespace heat {
 struct CtaMeta {            // one sample, prepared by the control warp
     int u, p, fresh, dup, H, done, pmult, regather;
     long long s;
+    float rH;
+    int pad;
     int negid[64];
 };
 
+constexpr int CTA_HIS_REGS = 4;                              // history ids per control-warp lane
+constexpr int CTA_HIS_MAX = 32 * CTA_HIS_REGS;              // max_his served from registers / shared memory
+
 template <int D, int NPS> struct CtaCfg {
     static constexpr int LPR = D / 4;                       // lanes per row
-    static constexpr int NSLOT = 18;
-    static constexpr int ROWT = NSLOT * LPR;
-    static constexpr int CTRL0 = (ROWT + 31) / 32 * 32;      // first thread of the control warp
+    static constexpr int NEGT = 16 * LPR;                    // threads of the negative slots (whole warps)
+    static constexpr int SLOTW = LPR < 32 ? 32 : LPR;        // threads reserved for the pos / usr slot (one warp)
+    static constexpr int POS0 = NEGT, USR0 = POS0 + SLOTW, CTRL0 = USR0 + SLOTW;
     static constexpr int NT = CTRL0 + 32;
+    static constexpr int NSLOT = 18;
     static constexpr int KMAX = 16 * NPS;
     static constexpr int GT = 4 * D;                         // GEMV / W0-accumulator threads
     static constexpr int IQ = D / 4;                         // W0 rows per GEMV thread
-    static_assert(GT <= ROWT, "GEMV threads are row threads");
+    static constexpr bool WREG = D <= 64;                    // W0 slice in registers (else shared memory)
+    static_assert(GT == NEGT, "GEMV threads are exactly the negative-slot threads");
     // shared memory, in floats
     static constexpr int OFF_W0 = 0;
-    static constexpr int OFF_MEAN = OFF_W0 + D * D;          // [2][D]
-    static constexpr int OFF_ACC = OFF_MEAN + 2 * D;         // [D] history column sums
+    static constexpr int OFF_MEAN = OFF_W0 + (WREG ? 0 : D * D);   // [3][D]
+    static constexpr int OFF_ACC = OFF_MEAN + 3 * D;         // [D] history column sums
     static constexpr int OFF_FPART = OFF_ACC + D;            // [4][D]
-    static constexpr int OFF_UA = OFF_FPART + 4 * D;         // [D] the user's stored row (input of the aggregation)
-    static constexpr int OFF_PW = OFF_UA + D;                // [D]
-    static constexpr int OFF_GP = OFF_PW + D;                // [D] (spare)
-    static constexpr int OFF_GU06 = OFF_GP + D;              // [D] 0.6 * user grad (W0 outer product)
+    static constexpr int OFF_UROW = OFF_FPART + 4 * D;       // [D] the user's stored row (input of the aggregation)
+    static constexpr int OFF_PW = OFF_UROW + D;              // [D] positive row snapshot (user step)
+    static constexpr int OFF_GU06 = OFF_PW + D;              // [D] 0.6 * user grad (W0 outer product)
     static constexpr int OFF_PART = OFF_GU06 + D;            // [16][D] user-grad partial sums of the negative slots
     static constexpr int OFF_HPART = OFF_PART + 16 * D;      // [NSLOT][D] history-gather partial sums
-    static constexpr int OFF_SC = OFF_HPART + NSLOT * D;     // un[KMAX], nn[KMAX], pp, up
-    static constexpr int OFF_META = OFF_SC + 2 * KMAX + 8;   // 2 x CtaMeta
+    static constexpr int OFF_SC = OFF_HPART + NSLOT * D;     // sE[16], sB[16], pp, up, Ep
+    static constexpr int OFF_HID = OFF_SC + 40;              // [2][CTA_HIS_MAX] history ids of the run (ints)
+    static constexpr int OFF_META = OFF_HID + 2 * CTA_HIS_MAX;   // 2 x CtaMeta
     static constexpr int FLOATS = OFF_META + 2 * (int)(sizeof(CtaMeta) / 4) + 8;
 };
 
 // Barrier over the row threads only (named barrier 1): the control warp is not on the critical path of
-// the sample being processed, it meets the row threads at the two full barriers [B] and [C].
+// the sample being processed, it meets the row threads at the full barrier [B].
 template <int NROW> __device__ __forceinline__ void row_bar(bool is_ctrl)
 {
     if (!is_ctrl) asm volatile("bar.sync 1, %0;" ::"n"(NROW) : "memory");
 }
 
-template <int VL> __device__ __forceinline__ float group_max(float v, unsigned mask)
+// N independent sums over the VL lanes of a row group in ONE butterfly: the N shuffles of a step are
+// issued back to back, so the latency of a step is paid once, not N times.
+template <int VL, int N> __device__ __forceinline__ void group_sum_n(float (&v)[N], unsigned mask)
 {
 #pragma unroll
-    for (int o = VL / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(mask, v, o));
-    return v;
+    for (int o = VL / 2; o > 0; o >>= 1) {
+        float t[N];
+#pragma unroll
+        for (int i = 0; i < N; ++i) t[i] = __shfl_xor_sync(mask, v[i], o);
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] += t[i];
+    }
 }
 
-// Control warp: fill `m` with the sample after (s_prev, chunk_end); fetches a new chunk when needed.
-// Carries the run state (cur_u, H, age, regather) in registers and returns the history multiplicity of
-// the sample's positive (for the patch of the cached column sums).
-template <int D, int NPS>
-__device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, int lane, long long &s, long long &s_end,
-                                            long long nchunks, int &cur_u, int &H, int &age, bool &regather, int &pmult,
-                                            bool no_cache)
+// max(x, eps)^-1/2 (matrix_factorization.cpp:50-53 clamps the squared norms at eps before the root)
+// as MUFU.RSQ + one Newton step (full fp32 accuracy without the division / square-root subroutines)
+__device__ __forceinline__ float rsqrt_eps(float x)
 {
-    constexpr int KMAX = 16 * NPS;
-    if (s >= s_end) {                                      // next chunk (warp-uniform)
-        unsigned long long c = 0;
-        if (lane == 0) c = atomicAdd(P.chunk_counter, 1ULL);
-        c = __shfl_sync(FULL, c, 0);
-        if ((long long)c >= nchunks) {
+    x = fmaxf(x, 1e-8f);
+    const float y = rsqrtf(x);
+    return y * fmaf(-0.5f * x * y, y, 1.5f);
+}
+
+// Control-warp state carried across samples.
+struct CtaCtrl {
+    long long s = 0, s_end = 0;
+    int cur_u = -1, ids_u = -1, H = 0, age = 0;
+    bool regather = false;
+    float rH = 0.f;
+    int2 nxt = make_int2(0, 0);                              // click of sample s (prefetched)
+    int hreg[CTA_HIS_REGS];                                  // history ids lane, lane+32, ... of user ids_u
+};
+
+// Control warp: fill `m` with the next sample of this CTA (fetches a new chunk when needed) and, when the
+// sample starts a run or re-gathers, publish the run's history ids in `hid_dst`.
+template <int D, int NPS>
+__device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, int *hid_dst, int lane, CtaCtrl &c,
+                                            long long nchunks, bool no_cache)
+{
+    if (c.s >= c.s_end) {                                  // next chunk (warp-uniform)
+        unsigned long long ch = 0;
+        if (lane == 0) ch = atomicAdd(P.chunk_counter, 1ULL);
+        ch = __shfl_sync(FULL, ch, 0);
+        if ((long long)ch >= nchunks) {
             if (lane == 0) m->done = 1;
             return;
         }
-        s = P.begin + (long long)c * P.chunk;
-        s_end = min(P.end, s + (long long)P.chunk);
-        cur_u = -1;
+        c.s = P.begin + (long long)ch * P.chunk;
+        c.s_end = min(P.end, c.s + (long long)P.chunk);
+        c.cur_u = -1;
+        c.nxt = __ldg(&P.clicks[c.s]);
     }
-    const int2 up = __ldg(&P.clicks[s]);
-    const int u = up.x, p = up.y;
+    const long long s = c.s;
+    const int u = c.nxt.x, p = c.nxt.y;
+    if (s + 1 < c.s_end) c.nxt = __ldg(&P.clicks[s + 1]);  // consumed by the next call
     const int K = P.K;
+    const bool big_his = P.max_his > CTA_HIS_MAX;
     bool dup = false, nhit = false;
     int myneg[NPS];
 #pragma unroll
@@ -124,74 +159,128 @@ __device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, in
         dup |= (lane < 16) && myneg[n] == p;
     }
     dup = __any_sync(FULL, dup);
-    const bool fresh = no_cache || u != cur_u || age >= 64 || regather;
-    if (fresh) { H = __ldg(P.masks + u); cur_u = u; age = 0; }
-    // history membership of the rows this sample rewrites (see train_kernel.cuh, CACHE)
-    pmult = 0;
-    const int *hrow = P.his + (size_t)u * P.max_his;
-    for (int c0 = 0; c0 < H; c0 += 16) {
-        const int hi = c0 + lane - 16;
-        const int hv = (lane >= 16 && hi < H) ? __ldg(hrow + hi) : (-1000 - lane);
-        pmult += __popc(__ballot_sync(FULL, hv == p));
+    const bool fresh = no_cache || u != c.cur_u || c.age >= 64 || c.regather;
+    if (fresh) {
+        if (u != c.ids_u) {                                // a new user: history length and ids
+            c.H = __ldg(P.masks + u);
+            c.rH = (float)(1.0 / (double)c.H);             // behavior_aggregators.cpp:63
+            c.ids_u = u;
+            if (!big_his) {
+                const int *hrow = P.his + (size_t)u * P.max_his;
 #pragma unroll
-        for (int n = 0; n < NPS; ++n) {
-            const unsigned mm = __match_any_sync(FULL, lane < 16 ? myneg[n] : hv);
-            nhit |= (lane < 16) && (mm >> 16) != 0;
+                for (int j = 0; j < CTA_HIS_REGS; ++j) {
+                    const int idx = lane + 32 * j;
+                    c.hreg[j] = idx < c.H ? __ldg(hrow + idx) : (-1000 - idx);
+                }
+            }
+        }
+        c.cur_u = u; c.age = 0;
+        if (!big_his) {
+#pragma unroll
+            for (int j = 0; j < CTA_HIS_REGS; ++j) hid_dst[lane + 32 * j] = c.hreg[j];
         }
     }
-    regather = __any_sync(FULL, nhit) || (pmult != 0 && dup);
-    age += 1;
-    if (lane == 0) { m->u = u; m->p = p; m->fresh = fresh; m->dup = dup; m->H = H; m->done = 0; m->s = s; m->pmult = pmult; m->regather = regather; }
-    (void)KMAX;
-    s += 1;
+    // history membership of the rows this sample rewrites (see train_kernel.cuh, CACHE)
+    int pmult = 0;
+    if (!big_his) {
+#pragma unroll
+        for (int j = 0; j < CTA_HIS_REGS; ++j) pmult += __popc(__ballot_sync(FULL, c.hreg[j] == p));
+#pragma unroll
+        for (int n = 0; n < NPS; ++n) {
+#pragma unroll
+            for (int t = 0; t < 16; ++t) {
+                const int v = __shfl_sync(FULL, myneg[n], t);
+#pragma unroll
+                for (int j = 0; j < CTA_HIS_REGS; ++j) nhit |= c.hreg[j] == v;
+            }
+        }
+    } else {
+        const int *hrow = P.his + (size_t)u * P.max_his;
+        for (int c0 = 0; c0 < c.H; c0 += 16) {
+            const int hi = c0 + lane - 16;
+            const int hv = (lane >= 16 && hi < c.H) ? __ldg(hrow + hi) : (-1000 - lane);
+            pmult += __popc(__ballot_sync(FULL, hv == p));
+#pragma unroll
+            for (int n = 0; n < NPS; ++n) {
+                const unsigned mm = __match_any_sync(FULL, lane < 16 ? myneg[n] : hv);
+                nhit |= (lane < 16) && (mm >> 16) != 0;
+            }
+        }
+    }
+    c.regather = __any_sync(FULL, nhit) || (pmult != 0 && dup);
+    c.age += 1;
+    if (lane == 0) {
+        m->u = u; m->p = p; m->fresh = fresh; m->dup = dup; m->H = c.H; m->done = 0; m->s = s;
+        m->pmult = pmult; m->regather = c.regather; m->rH = c.rH;
+    }
+    c.s = s + 1;
 }
 
+// Phase timing for kernel development (-DHEAT_CTA_PROFILE through HEAT_NVCC_DEFS, build.py): one thread of
+// neg slot 0, the pos slot, the usr slot and the control warp print clock64() at the marked points for a
+// few iterations of block 0.  (clock reads placed right after a barrier do not include the wait: the
+// barrier blocks the warp at its next dependent instruction; compare absolute times across warps.)
+#ifdef HEAT_CTA_PROFILE
+#define HEAT_PT(i) do { long long t_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) :: "memory"); if (prof_on) prof_abs[i] = t_; } while (0)
+#else
+#define HEAT_PT(i) do { } while (0)
+#endif
 
 template <int D, int NPS>
 __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const TrainParams P)
 {
     using C = CtaCfg<D, NPS>;
-    constexpr int LPR = C::LPR, NSLOT = C::NSLOT, KMAX = C::KMAX, IQ = C::IQ;
+    constexpr int LPR = C::LPR, NSLOT = C::NSLOT, IQ = C::IQ;
+    constexpr bool WREG = C::WREG;
     extern __shared__ __align__(16) float smem[];
     float *W0s = smem + C::OFF_W0, *meanb = smem + C::OFF_MEAN, *accs = smem + C::OFF_ACC, *fpart = smem + C::OFF_FPART;
-    float *urow_s = smem + C::OFF_UA, *pw_s = smem + C::OFF_PW, *gu06_s = smem + C::OFF_GU06;
+    float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW, *gu06_s = smem + C::OFF_GU06;
     float *part = smem + C::OFF_PART, *hpart = smem + C::OFF_HPART;
-    float *sc_un = smem + C::OFF_SC, *sc_nn = sc_un + KMAX, *sc3 = sc_nn + KMAX;
+    float *sE = smem + C::OFF_SC, *sB = sE + 16, *sc3 = sB + 16;      // sc3: pp, up, Ep
+    int *hid_s = reinterpret_cast<int *>(smem + C::OFF_HID);
     CtaMeta *meta = reinterpret_cast<CtaMeta *>(smem + C::OFF_META);
 
     const int tid = threadIdx.x, lane = tid & 31;
     const bool is_ctrl = tid >= C::CTRL0;
-    const bool is_row = tid < C::ROWT;
-    const int slot = tid / LPR, sl = tid % LPR;             // valid when is_row
-    const bool is_neg = is_row && slot < 16, is_pos = is_row && slot == 16, is_usr = is_row && slot == 17;
-    const bool is_gemv = tid < C::GT;
-    const int gj = tid % D, giq = tid / D;                   // GEMV column / row block (valid when is_gemv)
-    // lanes of this thread's row slot: slots of one warp take different branches, so every shuffle names its own group
-    const unsigned gmask = LPR >= 32 ? FULL : (((1u << (LPR & 31)) - 1u) << ((lane / LPR) * LPR));
-    const int gbase = (lane / LPR) * LPR;
+    const bool is_neg = tid < C::NEGT;                       // warp-uniform
+    const bool is_pos = tid >= C::POS0 && tid < C::POS0 + LPR;
+    const bool is_usr = tid >= C::USR0 && tid < C::USR0 + LPR;
+    const bool is_row = is_neg || is_pos || is_usr;
+    const int slot = is_neg ? tid / LPR : (is_pos ? 16 : 17), sl = tid % LPR;
+    const int gj = tid % D, giq = tid / D;                   // GEMV column / row block (neg threads)
+    const unsigned smask = LPR >= 32 ? FULL : ((1u << (LPR & 31)) - 1u);   // the pos / usr slot's lanes of its warp
 
-    for (int i = tid * 4; i < D * D; i += C::NT * 4) *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
-
-    const float gamma = 0.4f, omg = 1.0f - gamma, eps = 1e-8f;
+    const float gamma = 0.4f, omg = 1.0f - gamma;
     const float score_mul = (float)(1.0 / 0.07);
     const int K = P.K;
     const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
     const bool no_cache = P.no_cache != 0;
+    const bool big_his = P.max_his > CTA_HIS_MAX;
 
-    long long c_s = 0, c_end = 0;                            // control-warp state
-    int c_u = -1, c_H = 0, c_age = 0, c_pmult = 0;
-    bool c_regather = false;
-    float4 u_keep = f4zero(), gu_keep = f4zero();            // user slot: the run's user row / grad row
-    float w0acc[IQ];                                         // GEMV threads: W0 gradient accumulator
+    // this thread's slice of W0 (rows giq*IQ .. +IQ, column gj) and of its gradient accumulator
+    float wreg[WREG ? IQ : 1], w0acc[IQ];
 #pragma unroll
     for (int i = 0; i < IQ; ++i) w0acc[i] = 0.f;
+    if (WREG) {
+        if (is_neg) {
+#pragma unroll
+            for (int i = 0; i < IQ; ++i) wreg[WREG ? i : 0] = __ldcg(P.w0 + (giq * IQ + i) * D + gj);
+        }
+    } else {
+        for (int i = tid * 4; i < D * D; i += C::NT * 4) *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
+    }
+
+    CtaCtrl ctl;
+    float4 u_keep = f4zero(), gu_keep = f4zero();            // usr slot: the run's user row / grad row
     unsigned iter = 0;
     double loss_acc = 0.0;
+    float loss_f = 0.f;
     bool have_tail = false;                                  // W0 outer product of the previous sample pending
-    int cur = 0;
+    int cur = 0, mb = 0;                                     // meta buffer (2), mean buffer (3) of this sample
 
-    // W0 gradient of the sample whose mean is in `pm_all` (behavior_aggregators.cpp:131-146)
-    auto w0_tail = [&](const float *pm_all, bool flush, bool refresh_smem) {
+    // W0 gradient of the sample whose mean is `pm_all` (behavior_aggregators.cpp:131-146); every 32 samples
+    // the accumulated step is applied (W0 -= lr0 * acc / 32) and the thread's copy of W0 refreshed
+    auto w0_tail = [&](const float *pm_all, bool flush) {
         const float *pm = pm_all + giq * IQ;
         const float gq = gu06_s[gj];
 #pragma unroll
@@ -205,16 +294,20 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             for (int i = 0; i < IQ; ++i) {
                 const int e = (giq * IQ + i) * D + gj;
                 const float delta = -(P.lr_w0 * (w0acc[i] / 32.0f));
-                const float old = atomicAdd(P.w0 + e, delta);
-                if (refresh_smem) W0s[e] = old + delta;
+                const float old = atomicAdd(P.w0 + e, delta);    // returns the value before: picks up other CTAs' steps
+                if (WREG) wreg[WREG ? i : 0] = old + delta; else W0s[e] = old + delta;
                 w0acc[i] = 0.f;
             }
         }
     };
 
+#ifdef HEAT_CTA_PROFILE
+    const bool prof_on = blockIdx.x == 0 && (tid == 0 || tid == C::POS0 || tid == C::USR0 || tid == C::CTRL0);
+    long long prof_abs[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+#endif
     if (is_ctrl) {
         if (lane == 0) meta[0].done = 0;
-        cta_prepare<D, NPS>(P, &meta[0], lane, c_s, c_end, nchunks, c_u, c_H, c_age, c_regather, c_pmult, no_cache);
+        cta_prepare<D, NPS>(P, &meta[0], hid_s, lane, ctl, nchunks, no_cache);
     }
     __syncthreads();
 
@@ -223,8 +316,11 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         if (m->done) break;
         const int u = m->u, p = m->p, H = m->H;
         const bool fresh = m->fresh != 0, dup = m->dup != 0;
-        const float rH = (float)(1.0 / (double)H);          // behavior_aggregators.cpp:63
-        float *mean = meanb + cur * D;
+        const float rH = m->rH;
+        float *mean = meanb + mb * D;
+        const float *mean_prev = meanb + (mb == 0 ? 2 : mb - 1) * D;
+        float *mean_next = meanb + (mb == 2 ? 0 : mb + 1) * D;
+        HEAT_PT(0);
 
         // ---- issue the row loads of this sample
         int nid[NPS];
@@ -250,12 +346,18 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             }
             *reinterpret_cast<float4 *>(urow_s + 4 * sl) = rw;
         }
-        // ---- first sample of a run: gather the history rows (behavior_aggregators.cpp:96-105)
+        HEAT_PT(1);
+        // ---- first sample of a run: gather the history rows (behavior_aggregators.cpp:96-105); the ids come
+        //      from the control warp's copy in shared memory
         if (fresh) {
             if (is_row) {
-                const int *hrow = P.his + (size_t)u * P.max_his;
+                const int *hg = P.his + (size_t)u * P.max_his;
+                const int *hs = hid_s + cur * CTA_HIS_MAX;
                 float4 a4 = f4zero();
-                for (int h = slot; h < H; h += NSLOT) a4 = a4 + ldcg4(P.item_w + (size_t)__ldg(hrow + h) * D + 4 * sl);
+                for (int h = slot; h < H; h += NSLOT) {
+                    const int id = big_his ? __ldg(hg + h) : hs[h];
+                    a4 = a4 + ldcg4(P.item_w + (size_t)id * D + 4 * sl);
+                }
                 *reinterpret_cast<float4 *>(hpart + slot * D + 4 * sl) = a4;
             }
             row_bar<C::CTRL0>(is_ctrl);
@@ -271,108 +373,107 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         // ---- a W0 step is due (every 32 samples): it must land before this sample's mean.W0
         const bool flush_due = have_tail && (iter & 31) == 0;
         if (flush_due) {
-            row_bar<C::CTRL0>(is_ctrl);                       // the user slot has published 0.6*g_u of the previous sample
-            if (is_gemv) w0_tail(meanb + (cur ^ 1) * D, true, true);
+            row_bar<C::CTRL0>(is_ctrl);                       // the usr slot has published 0.6*g_u of the previous sample
+            if (is_neg) w0_tail(mean_prev, true);
         }
         // ---- f = mean . W0 as four partial GEMVs (behavior_aggregators.cpp:118)
-        if (is_gemv) {
+        if (is_neg) {
             const float *pm = mean + giq * IQ;
             float f0 = 0.f, f1 = 0.f, f2 = 0.f, f3 = 0.f;
 #pragma unroll
             for (int i4 = 0; i4 < IQ; i4 += 4) {
                 const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
-                const float *w = W0s + (giq * IQ + i4) * D + gj;
-                f0 = fmaf(m4.x, w[0], f0); f1 = fmaf(m4.y, w[D], f1); f2 = fmaf(m4.z, w[2 * D], f2); f3 = fmaf(m4.w, w[3 * D], f3);
+                if (WREG) {
+                    f0 = fmaf(m4.x, wreg[WREG ? i4 : 0], f0); f1 = fmaf(m4.y, wreg[WREG ? i4 + 1 : 0], f1);
+                    f2 = fmaf(m4.z, wreg[WREG ? i4 + 2 : 0], f2); f3 = fmaf(m4.w, wreg[WREG ? i4 + 3 : 0], f3);
+                } else {
+                    const float *w = W0s + (giq * IQ + i4) * D + gj;
+                    f0 = fmaf(m4.x, w[0], f0); f1 = fmaf(m4.y, w[D], f1); f2 = fmaf(m4.z, w[2 * D], f2); f3 = fmaf(m4.w, w[3 * D], f3);
+                }
             }
             fpart[giq * D + gj] = (f0 + f1) + (f2 + f3);
         }
+        HEAT_PT(2);
         // ---- control warp: prepare the next sample while this one is processed (meets the others at [B])
         if (is_ctrl) {
             if (lane == 0) meta[cur ^ 1].done = 0;
-            cta_prepare<D, NPS>(P, &meta[cur ^ 1], lane, c_s, c_end, nchunks, c_u, c_H, c_age, c_regather, c_pmult, no_cache);
+            cta_prepare<D, NPS>(P, &meta[cur ^ 1], hid_s + (cur ^ 1) * CTA_HIS_MAX, lane, ctl, nchunks, no_cache);
         }
+        HEAT_PT(3);
         row_bar<C::CTRL0>(is_ctrl);                                                   // [G1]
-        if (have_tail && !flush_due && is_gemv) w0_tail(meanb + (cur ^ 1) * D, false, false);
-        // ---- every row slot: u <- gamma*u + (1-gamma)*f (:122), uu
+        // ---- every row slot: u <- gamma*u + (1-gamma)*f (:122); its dots in one butterfly
+        //      (matrix_factorization.cpp:45-53, 82-85); E_k = exp(cos_k / T), published as per-slot sums
         float4 ua = f4zero();
-        float uu = 0.f;
+        float uu = 0.f, rinv_u = 0.f, pp = 0.f, upd = 0.f;
+        float un[NPS], nn[NPS], Ek[NPS], r3[NPS], rn3[NPS];
         if (is_row) {
             const float4 f0 = *reinterpret_cast<const float4 *>(fpart + 4 * sl), f1 = *reinterpret_cast<const float4 *>(fpart + D + 4 * sl);
             const float4 f2 = *reinterpret_cast<const float4 *>(fpart + 2 * D + 4 * sl), f3 = *reinterpret_cast<const float4 *>(fpart + 3 * D + 4 * sl);
             const float4 f = (f0 + f1) + (f2 + f3);
             ua = gamma * *reinterpret_cast<const float4 *>(urow_s + 4 * sl);
             fma4(ua, omg, f);
-            uu = group_sum<LPR>(dot4(ua, ua), gmask);
         }
-        // ---- dots (matrix_factorization.cpp:45-47, 82-85)
         if (is_neg) {
+            float r[1 + 2 * NPS];
+            r[0] = dot4(ua, ua);
+#pragma unroll
+            for (int n = 0; n < NPS; ++n) { r[1 + 2 * n] = dot4(ua, nw[n]); r[2 + 2 * n] = dot4(nw[n], nw[n]); }
+            group_sum_n<LPR, 1 + 2 * NPS>(r, FULL);
+            uu = r[0];
+            rinv_u = rsqrt_eps(uu);
+            float es = 0.f, bs = 0.f;
 #pragma unroll
             for (int n = 0; n < NPS; ++n) {
-                const int k = slot + 16 * n;
-                const float un_ = group_sum<LPR>(dot4(ua, nw[n]), gmask), nn_ = group_sum<LPR>(dot4(nw[n], nw[n]), gmask);
-                if (sl == 0 && k < K) { sc_un[k] = un_; sc_nn[k] = nn_; }
+                un[n] = r[1 + 2 * n]; nn[n] = r[2 + 2 * n];
+                const float rinv_n = rsqrt_eps(nn[n]);
+                Ek[n] = (slot + 16 * n < K) ? expf((un[n] * (rinv_u * rinv_n)) * score_mul) : 0.f;
+                r3[n] = (rinv_u * rinv_u) * (rinv_u * rinv_n);             // 1 / (|u|^3 |n|)   (:136)
+                rn3[n] = (rinv_u * rinv_n) * (rinv_n * rinv_n);            // 1 / (|u| |n|^3)   (:137)
+                es += Ek[n];
+                bs = fmaf(Ek[n], r3[n] * un[n], bs);
             }
+            if (sl == 0) { sE[slot] = es; sB[slot] = bs; }
         } else if (is_pos) {
-            const float pp_ = group_sum<LPR>(dot4(rw, rw), gmask), up_ = group_sum<LPR>(dot4(ua, rw), gmask);
-            if (sl == 0) { sc3[1] = pp_; sc3[2] = up_; }
+            float r[3] = {dot4(ua, ua), dot4(rw, rw), dot4(ua, rw)};
+            group_sum_n<LPR, 3>(r, smask);
+            uu = r[0]; pp = r[1]; upd = r[2];
+            rinv_u = rsqrt_eps(uu);
+            const float cos_p = upd * (rinv_u * rsqrt_eps(pp));
+            if (sl == 0) { sc3[0] = pp; sc3[1] = upd; sc3[2] = expf(-(cos_p * score_mul)); }
             *reinterpret_cast<float4 *>(pw_s + 4 * sl) = rw;
+        } else if (is_usr) {
+            float r[1] = {dot4(ua, ua)};
+            group_sum_n<LPR, 1>(r, smask);
+            uu = r[0];
+            rinv_u = rsqrt_eps(uu);
         }
+        HEAT_PT(4);
         row_bar<C::CTRL0>(is_ctrl);                                                   // [A]
-        // ---- scores and softmax, recomputed by every row slot from the shared scalars
-        //      (matrix_factorization.cpp:55-61, 91-109).  log(1 + sum_k exp(score_k)) is evaluated without
-        //      the reference's max shift: |score| <= 2/0.07, far inside fp32 range, same value to rounding.
-        float lgsum = 0.f, bsum = 0.f, esum = 0.f, unorm = 0.f, unorm3 = 0.f, pnorm = 0.f, pp = 0.f, upd = 0.f;
-        constexpr int SPL = (KMAX + LPR - 1) / LPR;
-        float k1[SPL], k2[SPL], k3[SPL];                       // per-k update coefficients, lane sl holds k = sl + LPR*q
+        // ---- softmax with the implicit zero logit (matrix_factorization.cpp:55-61, 91-109):
+        //      esum = 1 + sum_k exp((cos_k - cos_p)/T) = 1 + Ep * sum_k E_k;  lg_k = (E_k Ep / esum) / T.
+        //      No max shift: |cos/T| <= 14.3, far inside fp32 range.
+        float cE = 0.f, SE = 0.f, SB = 0.f, esum = 1.f;
         if (is_row) {
-            pp = sc3[1]; upd = sc3[2];
-            unorm = sqrtf(fmaxf(uu, eps)); pnorm = sqrtf(fmaxf(pp, eps));
-            unorm3 = unorm * unorm * unorm;
-            const float cos_p = upd / (unorm * pnorm);
-            float ev[SPL], r3[SPL], rn3[SPL], unv[SPL], nnv[SPL];
-#pragma unroll
-            for (int q = 0; q < SPL; ++q) {
-                const int k = sl + LPR * q;
-                ev[q] = 0.f; r3[q] = 0.f; rn3[q] = 0.f; unv[q] = 0.f; nnv[q] = 0.f;
-                if (k < K) {
-                    nnv[q] = sc_nn[k]; unv[q] = sc_un[k];
-                    const float nnorm = sqrtf(nnv[q] < eps ? eps : nnv[q]);
-                    ev[q] = expf((unv[q] / (unorm * nnorm) - cos_p) * score_mul);
-                    r3[q] = 1.f / (unorm3 * nnorm);                        // :136
-                    rn3[q] = 1.f / (unorm * (nnorm * nnorm * nnorm));      // :137
-                }
-                esum += ev[q];
-            }
-            esum = group_sum<LPR>(esum, gmask) + 1.0f;         // the implicit zero logit (:107)
-            const float inv_esum = 1.f / esum;
-#pragma unroll
-            for (int q = 0; q < SPL; ++q) {
-                const float lg = (ev[q] * inv_esum) * score_mul;   // :109
-                lgsum += lg; bsum = fmaf(lg, -(r3[q] * unv[q]), bsum);
-                k1[q] = lg * rn3[q] * nnv[q];                  // lg*gn_n = k1*u + k2*N[k] (:139,:143)
-                k2[q] = -(lg * rn3[q]) * unv[q];
-                k3[q] = lg * r3[q] * uu;                       // the N[k] part of lg*gu_n (:138,:141)
-            }
-            lgsum = group_sum<LPR>(lgsum, gmask);
-            bsum = group_sum<LPR>(bsum, gmask);
+            const float4 e0 = *reinterpret_cast<const float4 *>(sE), e1 = *reinterpret_cast<const float4 *>(sE + 4);
+            const float4 e2 = *reinterpret_cast<const float4 *>(sE + 8), e3 = *reinterpret_cast<const float4 *>(sE + 12);
+            const float4 e = (e0 + e1) + (e2 + e3);
+            SE = (e.x + e.y) + (e.z + e.w);
+            const float Ep = sc3[2];
+            esum = fmaf(Ep, SE, 1.0f);
+            cE = (Ep * score_mul) / esum;
         }
+        HEAT_PT(5);
         // ---- negative rows: grads, clipped step, write-back (:127-150; sgd.cpp:14-26)
+        //      lg*gn_n = c1*u + c2*N[k];  the N[k] part of lg*gu_n is c3*N[k] (:138-143)
+        float c1[NPS], c2[NPS];
         if (is_neg) {
             float4 gpart = f4zero();
-            float c1[NPS], c2[NPS];
 #pragma unroll
             for (int n = 0; n < NPS; ++n) {
-                const int k = slot + 16 * n;                   // its coefficients live in lane k % LPR, entry k / LPR
-                float c3 = 0.f;
-                c1[n] = 0.f; c2[n] = 0.f;
-#pragma unroll
-                for (int q = 0; q < SPL; ++q) {
-                    const float a1 = __shfl_sync(gmask, k1[q], gbase + (k % LPR));
-                    const float a2 = __shfl_sync(gmask, k2[q], gbase + (k % LPR));
-                    const float a3 = __shfl_sync(gmask, k3[q], gbase + (k % LPR));
-                    if (q == k / LPR && k < K) { c1[n] = a1; c2[n] = a2; c3 = a3; }
-                }
-                fma4(gpart, c3, nw[n]);
+                const float lg = cE * Ek[n];                   // :109
+                c1[n] = (lg * rn3[n]) * nn[n];
+                c2[n] = -(lg * rn3[n]) * un[n];
+                fma4(gpart, (lg * r3[n]) * uu, nw[n]);
             }
             *reinterpret_cast<float4 *>(part + slot * D + 4 * sl) = gpart;
             if (!dup) {
@@ -388,9 +489,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         stcg4(P.item_g + (size_t)nid[n] * D + 4 * sl, gk);   // :149
                     }
                 }
-            } else {                                         // keep the coefficients for the replay below
-#pragma unroll
-                for (int n = 0; n < NPS; ++n) gn[n] = make_float4(c1[n], c2[n], 0.f, 0.f);
             }
         }
         if (dup) {
@@ -403,7 +501,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         if (n == (k >> 4)) {
                             float *grow = P.item_g + (size_t)nid[n] * D + 4 * sl;
                             float4 gk = ldcg4(grow);
-                            fma4(gk, gn[n].x, ua); fma4(gk, gn[n].y, nw[n]);
+                            fma4(gk, c1[n], ua); fma4(gk, c2[n], nw[n]);
                             gk = clamp4(gk, P.clip);
                             float4 wk = nw[n];
                             fma4(wk, -P.lr, gk);
@@ -415,11 +513,13 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 row_bar<C::CTRL0>(is_ctrl);
             }
         }
-        // ---- positive row (:142, :169, :173-174); patch of the cached history sums
+        // ---- positive row (:142, :169, :173-174); patch of the cached history sums; loss (:108)
         if (is_pos) {
-            const float r_u_p3 = 1.f / (unorm * (pnorm * pnorm * pnorm));
+            const float rinv_p = rsqrt_eps(pp);
+            const float lgsum = cE * SE;
+            const float q = lgsum * ((rinv_u * rinv_p) * (rinv_p * rinv_p));   // lgsum / (|u| |p|^3)
             float4 gp = rg;
-            fma4(gp, -(lgsum * r_u_p3) * pp, ua); fma4(gp, (lgsum * r_u_p3) * upd, rw);   // lgsum * gp_p, gp_p = -(pp*u - up*p)*r
+            fma4(gp, -q * pp, ua); fma4(gp, q * upd, rw);          // lgsum * gp_p, gp_p = -(pp*u - up*p) / (|u||p|^3)
             gp = clamp4(gp, P.clip);
             float4 wp = rw;
             fma4(wp, -P.lr, gp);
@@ -430,24 +530,34 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             float4 a4 = *reinterpret_cast<const float4 *>(accs + 4 * sl);
             fma4(a4, m->regather ? 0.f : -P.lr * (float)m->pmult, gp);
             *reinterpret_cast<float4 *>(accs + 4 * sl) = a4;
-            *reinterpret_cast<float4 *>(meanb + (cur ^ 1) * D + 4 * sl) = rH * a4;
+            *reinterpret_cast<float4 *>(mean_next + 4 * sl) = rH * a4;
             if (sl == 0) {
-                const float loss = logf(esum);                   // :108
-                loss_acc += (double)loss;
+                const float loss = logf(esum);
+                loss_f += loss;
+                if ((iter & 31) == 31) { loss_acc += (double)loss_f; loss_f = 0.f; }
                 if (P.loss_out) P.loss_out[m->s - P.begin] = loss;
             }
         }
+        // ---- W0 outer product of the PREVIOUS sample (its 0.6*g_u was published before [G1])
+        if (have_tail && !flush_due && is_neg) w0_tail(mean_prev, false);
+        HEAT_PT(6);
         __syncthreads();                                                              // [B]
         // ---- user row: grad, aggregator backward, step (:141, :152, :166, :171-172); overlaps the next sample's loads
         if (is_usr) {
+            const float4 b0 = *reinterpret_cast<const float4 *>(sB), b1 = *reinterpret_cast<const float4 *>(sB + 4);
+            const float4 b2 = *reinterpret_cast<const float4 *>(sB + 8), b3 = *reinterpret_cast<const float4 *>(sB + 12);
+            const float4 b = (b0 + b1) + (b2 + b3);
+            SB = (b.x + b.y) + (b.z + b.w);
+            pp = sc3[0]; upd = sc3[1];
             float4 gacc = f4zero();
 #pragma unroll
             for (int q = 0; q < 16; ++q) gacc = gacc + *reinterpret_cast<const float4 *>(part + q * D + 4 * sl);
             const float4 pw = *reinterpret_cast<const float4 *>(pw_s + 4 * sl);
-            const float r_u3_p = 1.f / (unorm3 * pnorm);
-            // + sum_k lg_k*(-r*un_k)*u  - lgsum*gu_p,  gu_p = (uu*p - up*u)*r_u3_p  (:60-62)
-            fma4(gacc, bsum + lgsum * r_u3_p * upd, ua);
-            fma4(gacc, -(lgsum * r_u3_p) * uu, pw);
+            const float lgsum = cE * SE;
+            const float q3 = lgsum * ((rinv_u * rinv_u) * (rinv_u * rsqrt_eps(pp)));   // lgsum / (|u|^3 |p|)
+            // sum_k lg_k*(-un_k/(|u|^3|n_k|))*u  - lgsum*gu_p,  gu_p = (uu*p - up*u)/(|u|^3|p|)  (:60-62)
+            fma4(gacc, fmaf(q3, upd, -(cE * SB)), ua);
+            fma4(gacc, -q3 * uu, pw);
             float4 gu = rg + gacc;
             *reinterpret_cast<float4 *>(gu06_s + 4 * sl) = omg * gu;      // behavior_aggregators.cpp:131-139
             gu = gamma * gu;                                               // :148-152
@@ -457,14 +567,25 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
             u_keep = ua; gu_keep = gu;
         }
+        HEAT_PT(7);
+#ifdef HEAT_CTA_PROFILE
+        if (prof_on && iter >= 1000 && iter < 1004)
+            printf("abs tid %d iter %u fresh %d dup %d: top %lld issue %lld gemv %lld prep %lld dots %lld softmax %lld update %lld user %lld\n", tid, iter, (int)fresh, (int)dup,
+                   prof_abs[0] % 1000000, prof_abs[1] % 1000000, prof_abs[2] % 1000000, prof_abs[3] % 1000000, prof_abs[4] % 1000000, prof_abs[5] % 1000000,
+                   prof_abs[6] % 1000000, prof_abs[7] % 1000000);
+#endif
         iter += 1;
         have_tail = true;
         cur ^= 1;
+        mb = (mb == 2) ? 0 : mb + 1;
     }
     // ---- W0 gradient of the last sample and the leftover (< 32 samples) accumulators
     __syncthreads();
-    if (have_tail && is_gemv) w0_tail(meanb + (cur ^ 1) * D, ((iter & 31) == 0) || !P.drop_w0_tail, false);
-    if (is_pos && sl == 0 && loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
+    if (have_tail && is_neg) w0_tail(meanb + (mb == 0 ? 2 : mb - 1) * D, ((iter & 31) == 0) || !P.drop_w0_tail);
+    if (is_pos && sl == 0) {
+        loss_acc += (double)loss_f;
+        if (loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
+    }
 }
 
 }  // namespace heat
