@@ -34,7 +34,7 @@ struct CtaMeta {            // one sample, prepared by the control warp
     int u, p, fresh, dup, H, done, pmult, regather;
     long long s;
     float rH;
-    int pad;
+    int late;               // shares an item row with the previous sample: its rows may not be prefetched
     int negid[64];
 };
 
@@ -52,6 +52,7 @@ template <int D, int NPS> struct CtaCfg {
     static constexpr int GT = 4 * D;                         // GEMV / W0-accumulator threads
     static constexpr int IQ = D / 4;                         // W0 rows per GEMV thread
     static constexpr bool WREG = D <= 64;                    // W0 slice in registers (else shared memory)
+    static constexpr bool PF = D <= 64;                      // rows of the next sample prefetched (cp.async) during this one
     static_assert(GT == NEGT, "GEMV threads are exactly the negative-slot threads");
     // shared memory, in floats
     static constexpr int OFF_W0 = 0;
@@ -64,9 +65,10 @@ template <int D, int NPS> struct CtaCfg {
     static constexpr int OFF_PART = OFF_GU06 + D;            // [16][D] user-grad partial sums of the negative slots
     static constexpr int OFF_HPART = OFF_PART + 16 * D;      // [NSLOT][D] history-gather partial sums
     static constexpr int OFF_SC = OFF_HPART + NSLOT * D;     // sE[16], sB[16], pp, up, Ep
-    static constexpr int OFF_HID = OFF_SC + 40;              // [2][CTA_HIS_MAX] history ids of the run (ints)
-    static constexpr int OFF_META = OFF_HID + 2 * CTA_HIS_MAX;   // 2 x CtaMeta
-    static constexpr int FLOATS = OFF_META + 2 * (int)(sizeof(CtaMeta) / 4) + 8;
+    static constexpr int OFF_HID = OFF_SC + 40;              // [3][CTA_HIS_MAX] history ids of the run (ints)
+    static constexpr int OFF_META = OFF_HID + 3 * CTA_HIS_MAX;   // 3 x CtaMeta (this sample, next, the one being prepared)
+    static constexpr int OFF_STAGE = OFF_META + 3 * (int)(sizeof(CtaMeta) / 4) + 8;   // [2*NPS][CTRL0] float4: prefetched rows
+    static constexpr int FLOATS = OFF_STAGE + (PF ? 2 * NPS * CTRL0 * 4 : 0);
 };
 
 // Barrier over the row threads only (named barrier 1): the control warp is not on the critical path of
@@ -99,20 +101,33 @@ __device__ __forceinline__ float rsqrt_eps(float x)
     return y * fmaf(-0.5f * x * y, y, 1.5f);
 }
 
+// 16-byte asynchronous copy global -> shared (LDGSTS, L2-coherent): the row prefetch.  Every thread copies
+// exactly the slice it consumes later, so completion needs no cross-thread synchronisation.
+__device__ __forceinline__ void cp_async16(float *smem_dst, const float *gsrc)
+{
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // Control-warp state carried across samples.
-struct CtaCtrl {
+template <int NPS> struct CtaCtrl {
     long long s = 0, s_end = 0;
     int cur_u = -1, ids_u = -1, H = 0, age = 0;
     bool regather = false;
     float rH = 0.f;
-    int2 nxt = make_int2(0, 0);                              // click of sample s (prefetched)
+    long long blk0 = 0;                                      // lane holds click blk0 + lane (clk) and blk0 + 32 + lane (clkn)
+    int2 clk = make_int2(0, 0), clkn = make_int2(0, 0);
     int hreg[CTA_HIS_REGS];                                  // history ids lane, lane+32, ... of user ids_u
+    int prevneg[NPS];                                        // ids of the previously prepared sample
+    int prev_p = -5000;
 };
 
 // Control warp: fill `m` with the next sample of this CTA (fetches a new chunk when needed) and, when the
 // sample starts a run or re-gathers, publish the run's history ids in `hid_dst`.
 template <int D, int NPS>
-__device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, int *hid_dst, int lane, CtaCtrl &c,
+__device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, int *hid_dst, int lane, CtaCtrl<NPS> &c,
                                             long long nchunks, bool no_cache)
 {
     if (c.s >= c.s_end) {                                  // next chunk (warp-uniform)
@@ -126,11 +141,16 @@ __device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, in
         c.s = P.begin + (long long)ch * P.chunk;
         c.s_end = min(P.end, c.s + (long long)P.chunk);
         c.cur_u = -1;
-        c.nxt = __ldg(&P.clicks[c.s]);
+        c.blk0 = c.s;
+        c.clk = (c.s + lane < c.s_end) ? __ldg(&P.clicks[c.s + lane]) : make_int2(0, 0);
+        c.clkn = (c.s + 32 + lane < c.s_end) ? __ldg(&P.clicks[c.s + 32 + lane]) : make_int2(0, 0);
+    } else if (c.s - c.blk0 == 32) {                       // next block of 32 clicks of this chunk
+        c.blk0 = c.s;
+        c.clk = c.clkn;
+        c.clkn = (c.s + 32 + lane < c.s_end) ? __ldg(&P.clicks[c.s + 32 + lane]) : make_int2(0, 0);
     }
     const long long s = c.s;
-    const int u = c.nxt.x, p = c.nxt.y;
-    if (s + 1 < c.s_end) c.nxt = __ldg(&P.clicks[s + 1]);  // consumed by the next call
+    const int u = __shfl_sync(FULL, c.clk.x, (int)(s - c.blk0)), p = __shfl_sync(FULL, c.clk.y, (int)(s - c.blk0));
     const int K = P.K;
     const bool big_his = P.max_his > CTA_HIS_MAX;
     bool dup = false, nhit = false;
@@ -159,6 +179,21 @@ __device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, in
         dup |= (lane < 16) && myneg[n] == p;
     }
     dup = __any_sync(FULL, dup);
+    // an item row shared with the previously prepared sample (which rewrites it): no prefetch
+    bool conf = p == c.prev_p;
+#pragma unroll
+    for (int n = 0; n < NPS; ++n) {
+#pragma unroll
+        for (int n2 = 0; n2 < NPS; ++n2) {
+            const unsigned mm = __match_any_sync(FULL, lane < 16 ? myneg[n] : c.prevneg[n2]);
+            conf |= (lane < 16) && myneg[n] >= 0 && (mm >> 16) != 0;
+        }
+        conf |= myneg[n] == c.prev_p || c.prevneg[n] == p;
+    }
+    const bool late = __any_sync(FULL, conf);
+#pragma unroll
+    for (int n = 0; n < NPS; ++n) c.prevneg[n] = myneg[n];
+    c.prev_p = p;
     const bool fresh = no_cache || u != c.cur_u || c.age >= 64 || c.regather;
     if (fresh) {
         if (u != c.ids_u) {                                // a new user: history length and ids
@@ -211,7 +246,7 @@ __device__ __forceinline__ void cta_prepare(const TrainParams &P, CtaMeta *m, in
     c.age += 1;
     if (lane == 0) {
         m->u = u; m->p = p; m->fresh = fresh; m->dup = dup; m->H = c.H; m->done = 0; m->s = s;
-        m->pmult = pmult; m->regather = c.regather; m->rH = c.rH;
+        m->pmult = pmult; m->regather = c.regather; m->rH = c.rH; m->late = late;
     }
     c.s = s + 1;
 }
@@ -231,7 +266,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
 {
     using C = CtaCfg<D, NPS>;
     constexpr int LPR = C::LPR, NSLOT = C::NSLOT, IQ = C::IQ;
-    constexpr bool WREG = C::WREG;
+    constexpr bool WREG = C::WREG, PF = C::PF;
     extern __shared__ __align__(16) float smem[];
     float *W0s = smem + C::OFF_W0, *meanb = smem + C::OFF_MEAN, *accs = smem + C::OFF_ACC, *fpart = smem + C::OFF_FPART;
     float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW, *gu06_s = smem + C::OFF_GU06;
@@ -239,6 +274,8 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     float *sE = smem + C::OFF_SC, *sB = sE + 16, *sc3 = sB + 16;      // sc3: pp, up, Ep
     int *hid_s = reinterpret_cast<int *>(smem + C::OFF_HID);
     CtaMeta *meta = reinterpret_cast<CtaMeta *>(smem + C::OFF_META);
+    float *stage = smem + C::OFF_STAGE + 4 * threadIdx.x;    // this thread's prefetch slots: [2*n] weight, [2*n+1] grad slice
+    constexpr int STG = C::CTRL0 * 4;                        // floats between two slots
 
     const int tid = threadIdx.x, lane = tid & 31;
     const bool is_ctrl = tid >= C::CTRL0;
@@ -270,13 +307,18 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         for (int i = tid * 4; i < D * D; i += C::NT * 4) *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
     }
 
-    CtaCtrl ctl;
-    float4 u_keep = f4zero(), gu_keep = f4zero();            // usr slot: the run's user row / grad row
+    CtaCtrl<NPS> ctl;
+#pragma unroll
+    for (int n = 0; n < NPS; ++n) ctl.prevneg[n] = -2000 - n;
+    float4 u_keep = f4zero(), gu_keep = f4zero();            // usr slot: the row / grad row of user keep_u after its last step
+    int keep_u = -1, pf_u = -1;                              // usr slot: user of u_keep; user whose row is in the prefetch slot
+    bool have_pf = false;                                    // the prefetch slots hold this sample's item rows
+    int nidn[NPS];
     unsigned iter = 0;
     double loss_acc = 0.0;
     float loss_f = 0.f;
     bool have_tail = false;                                  // W0 outer product of the previous sample pending
-    int cur = 0, mb = 0;                                     // meta buffer (2), mean buffer (3) of this sample
+    int cur = 0, mb = 0;                                     // meta / history-id buffer and mean buffer of this sample (rings of 3)
 
     // W0 gradient of the sample whose mean is `pm_all` (behavior_aggregators.cpp:131-146); every 32 samples
     // the accumulated step is applied (W0 -= lr0 * acc / 32) and the thread's copy of W0 refreshed
@@ -302,12 +344,14 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     };
 
 #ifdef HEAT_CTA_PROFILE
-    const bool prof_on = blockIdx.x == 0 && (tid == 0 || tid == C::POS0 || tid == C::USR0 || tid == C::CTRL0);
+    const bool prof_on = blockIdx.x == 0 && lane == 0;
     long long prof_abs[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 #endif
     if (is_ctrl) {
         if (lane == 0) meta[0].done = 0;
         cta_prepare<D, NPS>(P, &meta[0], hid_s, lane, ctl, nchunks, no_cache);
+        if (lane == 0) meta[1].done = 0;
+        cta_prepare<D, NPS>(P, &meta[1], hid_s + CTA_HIS_MAX, lane, ctl, nchunks, no_cache);
     }
     __syncthreads();
 
@@ -322,30 +366,73 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         float *mean_next = meanb + (mb == 2 ? 0 : mb + 1) * D;
         HEAT_PT(0);
 
-        // ---- issue the row loads of this sample
+        // ---- the rows of this sample: prefetched during the previous sample, or loaded now
+        const int nx = cur == 2 ? 0 : cur + 1, n2 = nx == 2 ? 0 : nx + 1;
+        const CtaMeta *mn = &meta[nx];
+        const bool pf = PF && !mn->done && !mn->late;          // block-uniform
         int nid[NPS];
         float4 nw[NPS], gn[NPS];
         float4 rw = f4zero(), rg = f4zero();                  // positive / user weight and grad slices
         if (is_neg) {
+            if (have_pf) cp_async_wait0();
 #pragma unroll
             for (int n = 0; n < NPS; ++n) {
                 const int k = slot + 16 * n;
-                nid[n] = k < K ? m->negid[k] : 0;
-                nw[n] = k < K ? ldcg4(P.item_w + (size_t)nid[n] * D + 4 * sl) : f4zero();
-                gn[n] = k < K ? ldcg4(P.item_g + (size_t)nid[n] * D + 4 * sl) : f4zero();
+                if (have_pf) {
+                    nid[n] = nidn[n];
+                    nw[n] = k < K ? *reinterpret_cast<const float4 *>(stage + (2 * n) * STG) : f4zero();
+                    gn[n] = k < K ? *reinterpret_cast<const float4 *>(stage + (2 * n + 1) * STG) : f4zero();
+                } else {
+                    nid[n] = k < K ? m->negid[k] : 0;
+                    nw[n] = k < K ? ldcg4(P.item_w + (size_t)nid[n] * D + 4 * sl) : f4zero();
+                    gn[n] = k < K ? ldcg4(P.item_g + (size_t)nid[n] * D + 4 * sl) : f4zero();
+                }
+            }
+            if (pf) {
+#pragma unroll
+                for (int n = 0; n < NPS; ++n) {
+                    const int k = slot + 16 * n;
+                    nidn[n] = k < K ? mn->negid[k] : 0;
+                    if (k < K) {
+                        cp_async16(stage + (2 * n) * STG, P.item_w + (size_t)nidn[n] * D + 4 * sl);
+                        cp_async16(stage + (2 * n + 1) * STG, P.item_g + (size_t)nidn[n] * D + 4 * sl);
+                    }
+                }
+                cp_async_commit();
             }
         } else if (is_pos) {
-            rw = ldcg4(P.item_w + (size_t)p * D + 4 * sl);
-            rg = ldcg4(P.item_g + (size_t)p * D + 4 * sl);
+            if (have_pf) {
+                cp_async_wait0();
+                rw = *reinterpret_cast<const float4 *>(stage); rg = *reinterpret_cast<const float4 *>(stage + STG);
+            } else {
+                rw = ldcg4(P.item_w + (size_t)p * D + 4 * sl);
+                rg = ldcg4(P.item_g + (size_t)p * D + 4 * sl);
+            }
+            if (pf) {
+                cp_async16(stage, P.item_w + (size_t)mn->p * D + 4 * sl);
+                cp_async16(stage + STG, P.item_g + (size_t)mn->p * D + 4 * sl);
+                cp_async_commit();
+            }
         } else if (is_usr) {
-            if (fresh) {
+            if (!fresh || u == keep_u) {                      // the run continues: the row is in registers
+                rw = u_keep; rg = gu_keep;
+            } else if (pf_u == u) {
+                cp_async_wait0();
+                rw = *reinterpret_cast<const float4 *>(stage); rg = *reinterpret_cast<const float4 *>(stage + STG);
+            } else {
                 rw = ldcg4(P.user_w + (size_t)u * D + 4 * sl);
                 rg = ldcg4(P.user_g + (size_t)u * D + 4 * sl);
-            } else {
-                rw = u_keep; rg = gu_keep;
             }
             *reinterpret_cast<float4 *>(urow_s + 4 * sl) = rw;
+            pf_u = -1;
+            if (pf && mn->fresh && mn->u != u) {              // the next sample starts another user's run
+                pf_u = mn->u;
+                cp_async16(stage, P.user_w + (size_t)pf_u * D + 4 * sl);
+                cp_async16(stage + STG, P.user_g + (size_t)pf_u * D + 4 * sl);
+                cp_async_commit();
+            }
         }
+        have_pf = pf;
         HEAT_PT(1);
         // ---- first sample of a run: gather the history rows (behavior_aggregators.cpp:96-105); the ids come
         //      from the control warp's copy in shared memory
@@ -376,6 +463,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             row_bar<C::CTRL0>(is_ctrl);                       // the usr slot has published 0.6*g_u of the previous sample
             if (is_neg) w0_tail(mean_prev, true);
         }
+        HEAT_PT(8);
         // ---- f = mean . W0 as four partial GEMVs (behavior_aggregators.cpp:118)
         if (is_neg) {
             const float *pm = mean + giq * IQ;
@@ -394,10 +482,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             fpart[giq * D + gj] = (f0 + f1) + (f2 + f3);
         }
         HEAT_PT(2);
-        // ---- control warp: prepare the next sample while this one is processed (meets the others at [B])
+        // ---- control warp: prepare the sample after the next while this one is processed (meets the others at [B])
         if (is_ctrl) {
-            if (lane == 0) meta[cur ^ 1].done = 0;
-            cta_prepare<D, NPS>(P, &meta[cur ^ 1], hid_s + (cur ^ 1) * CTA_HIS_MAX, lane, ctl, nchunks, no_cache);
+            if (lane == 0) meta[n2].done = 0;
+            cta_prepare<D, NPS>(P, &meta[n2], hid_s + n2 * CTA_HIS_MAX, lane, ctl, nchunks, no_cache);
         }
         HEAT_PT(3);
         row_bar<C::CTRL0>(is_ctrl);                                                   // [G1]
@@ -413,6 +501,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             ua = gamma * *reinterpret_cast<const float4 *>(urow_s + 4 * sl);
             fma4(ua, omg, f);
         }
+#ifdef HEAT_CTA_PROFILE
+        if (ua.x == 123.456f) ua.y = 0.f;                     // force ua to be materialised here
+#endif
+        HEAT_PT(9);
         if (is_neg) {
             float r[1 + 2 * NPS];
             r[0] = dot4(ua, ua);
@@ -443,8 +535,16 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             *reinterpret_cast<float4 *>(pw_s + 4 * sl) = rw;
         } else if (is_usr) {
             float r[1] = {dot4(ua, ua)};
+#ifdef HEAT_CTA_PROFILE
+            if (r[0] == 123.456f) r[0] = 0.f;
+#endif
+            HEAT_PT(10);
             group_sum_n<LPR, 1>(r, smask);
             uu = r[0];
+#ifdef HEAT_CTA_PROFILE
+            if (uu == 123.456f) uu = 0.f;
+#endif
+            HEAT_PT(11);
             rinv_u = rsqrt_eps(uu);
         }
         HEAT_PT(4);
@@ -565,18 +665,18 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             fma4(ua, -P.lr, gu);
             stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
             stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
-            u_keep = ua; gu_keep = gu;
+            u_keep = ua; gu_keep = gu; keep_u = u;
         }
         HEAT_PT(7);
 #ifdef HEAT_CTA_PROFILE
-        if (prof_on && iter >= 1000 && iter < 1004)
-            printf("abs tid %d iter %u fresh %d dup %d: top %lld issue %lld gemv %lld prep %lld dots %lld softmax %lld update %lld user %lld\n", tid, iter, (int)fresh, (int)dup,
+        if (prof_on && iter == 1000)
+            printf("abs tid %d iter %u fresh %d dup %d: top %lld issue %lld gemv %lld prep %lld dots %lld softmax %lld update %lld user %lld pregemv %lld ua %lld dot %lld bfly %lld\n", tid, iter, (int)fresh, (int)dup,
                    prof_abs[0] % 1000000, prof_abs[1] % 1000000, prof_abs[2] % 1000000, prof_abs[3] % 1000000, prof_abs[4] % 1000000, prof_abs[5] % 1000000,
-                   prof_abs[6] % 1000000, prof_abs[7] % 1000000);
+                   prof_abs[6] % 1000000, prof_abs[7] % 1000000, prof_abs[8] % 1000000, prof_abs[9] % 1000000, prof_abs[10] % 1000000, prof_abs[11] % 1000000);
 #endif
         iter += 1;
         have_tail = true;
-        cur ^= 1;
+        cur = nx;
         mb = (mb == 2) ? 0 : mb + 1;
     }
     // ---- W0 gradient of the last sample and the leftover (< 32 samples) accumulators
