@@ -47,35 +47,38 @@ template <int NPS> struct CtaBatch {
 };
 
 template <int D, int NPS> struct CtaCfg {
+    static_assert(D == 32 || D == 64, "the CTA engine covers emb_dim 32 and 64 (W0 halves live in the pos / usr warps' registers)");
     static constexpr int LPR = D / 4;                       // lanes per row
     static constexpr int NEGT = 16 * LPR;                    // threads of the negative slots (whole warps)
-    static constexpr int SLOTW = LPR < 32 ? 32 : LPR;        // threads of the pos / usr role (whole warps)
-    static constexpr int POS0 = NEGT, USR0 = POS0 + SLOTW, CTRL0 = USR0 + SLOTW;
+    static constexpr int POS0 = NEGT, USR0 = POS0 + 32, CTRL0 = USR0 + 32;
     static constexpr int NT = CTRL0 + 32;
     static constexpr int NSLOT = 18;
     static constexpr int KMAX = 16 * NPS;
-    static constexpr int IQ = D / 4;                         // W0 rows per GEMV thread
-    static constexpr bool WREG = D <= 64;                    // W0 slice in registers (else shared memory)
-    static constexpr bool PF = D <= 64;                      // rows of the next sample prefetched during this one
+    static constexpr int IQ = D / 4;                         // W0 rows per thread in the batched W0 step (neg threads)
+    static constexpr int LC = 64 / D;                        // GEMV: lanes per column (pos / usr warp, D/2 columns each)
+    static constexpr int RL = D / LC;                        // GEMV: W0 rows per lane
+    static constexpr int MRING = 64, GRING = 32;             // history means of the last 64 samples, 0.6*g_u of the last 32
     // shared memory, in floats
-    static constexpr int OFF_W0 = 0;
-    static constexpr int OFF_MEAN = OFF_W0 + (WREG ? 0 : D * D);   // [3][D] history mean of samples it, it+1, it+2
-    static constexpr int OFF_ACC = OFF_MEAN + 3 * D;         // [D] history column sums
+    static constexpr int OFF_MEAN = 0;                       // [MRING][D]
+    static constexpr int OFF_GU06 = OFF_MEAN + MRING * D;    // [GRING][D] 0.6 * user grad (W0 outer products)
+    static constexpr int OFF_ACC = OFF_GU06 + GRING * D;     // [D] history column sums
     static constexpr int OFF_F = OFF_ACC + D;                // [D] f = mean . W0
     static constexpr int OFF_UROW = OFF_F + D;               // [D] the user's stored row (input of the aggregation)
     static constexpr int OFF_PW = OFF_UROW + D;              // [D] positive row snapshot (user step)
-    static constexpr int OFF_GU06 = OFF_PW + D;              // [2][D] 0.6 * user grad (W0 outer product)
-    static constexpr int OFF_PART = OFF_GU06 + 2 * D;        // [16][D] user-grad partial sums of the negative slots
+    static constexpr int OFF_PART = OFF_PW + D;              // [16][D] unnormalised user-grad partial sums of the negative slots
     static constexpr int OFF_HPART = OFF_PART + 16 * D;      // [NSLOT][D] history-gather partial sums
     static constexpr int OFF_SC = OFF_HPART + NSLOT * D;     // sE[16], sB[16], pp, up, Ep
     static constexpr int OFF_RING = OFF_SC + 40;             // 3 x CtaBatch
     static constexpr int OFF_STAGE = OFF_RING + 3 * (int)(sizeof(CtaBatch<NPS>) / 4);   // [2*NPS][CTRL0] float4: prefetched rows
-    static constexpr int FLOATS = OFF_STAGE + (PF ? 2 * NPS * CTRL0 * 4 : 0) + 8;
+    static constexpr int FLOATS = OFF_STAGE + 2 * NPS * CTRL0 * 4 + 8;
 };
 
-// named barriers: 1 = the row warps, 2 = row warps + control warp (once per batch)
+// named barriers: 1 = the row warps, 2 = row warps + control warp (once per batch),
+// 3 = pos warp (arrives: the next history mean is published) + usr warp (waits for it)
 template <int N> __device__ __forceinline__ void row_bar() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
 template <int N> __device__ __forceinline__ void batch_bar() { asm volatile("bar.sync 2, %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void mean_arrive() { asm volatile("bar.arrive 3, 64;" ::: "memory"); }
+__device__ __forceinline__ void mean_wait() { asm volatile("bar.sync 3, 64;" ::: "memory"); }
 
 // N independent sums over the VL lanes of a row group in ONE butterfly: the N shuffles of a step are
 // issued back to back, so the latency of a step is paid once, not N times.
@@ -218,15 +221,25 @@ __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch
     c.s += cnt;
 }
 
+
+// Phase timing for kernel development (-DHEAT_CTA_PROFILE through HEAT_NVCC_DEFS, build.py): lane 0 of every
+// row warp of block 0 prints clock64() at the marked points of one iteration.  (A clock read placed right
+// after a barrier does not include the wait; compare absolute times across warps.)
+#ifdef HEAT_CTA_PROFILE
+#define HEAT_PT(i) do { long long t_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) :: "memory"); if (prof_on) prof_abs[i] = t_; } while (0)
+#else
+#define HEAT_PT(i) do { } while (0)
+#endif
+
 template <int D, int NPS>
 __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const TrainParams P)
 {
     using C = CtaCfg<D, NPS>;
     constexpr int LPR = C::LPR, NSLOT = C::NSLOT, IQ = C::IQ, NROW = C::CTRL0, NT = C::NT;
-    constexpr bool WREG = C::WREG, PF = C::PF;
+    constexpr int LC = C::LC, RL = C::RL, MRING = C::MRING, GRING = C::GRING;
     extern __shared__ __align__(16) float smem[];
-    float *W0s = smem + C::OFF_W0, *meanb = smem + C::OFF_MEAN, *accs = smem + C::OFF_ACC, *f_s = smem + C::OFF_F;
-    float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW, *gu06_s = smem + C::OFF_GU06;
+    float *mean_ring = smem + C::OFF_MEAN, *gu06_ring = smem + C::OFF_GU06, *accs = smem + C::OFF_ACC, *f_s = smem + C::OFF_F;
+    float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW;
     float *part = smem + C::OFF_PART, *hpart = smem + C::OFF_HPART;
     float *sE = smem + C::OFF_SC, *sB = sE + 16, *sc3 = sB + 16;      // sc3: pp, up, Ep
     CtaBatch<NPS> *ring = reinterpret_cast<CtaBatch<NPS> *>(smem + C::OFF_RING);
@@ -263,7 +276,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     // ======== row warps ========
     const int sl = tid % LPR;                                // lane within the row slot (the pos / usr warps mirror their slot)
     const int slot = role == 0 ? tid / LPR : 15 + role;      // 0..15 negatives, 16 positive, 17 user
-    const int col = tid >> 2, rb = tid & 3;                  // GEMV: column / row block of this thread (neg warps)
     float *stage = smem + C::OFF_STAGE + 4 * tid;            // this thread's prefetch slots: [2n] weight, [2n+1] grad slice
     constexpr int STG = NROW * 4;                            // floats between two slots
 
@@ -271,60 +283,49 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     const float score_mul = (float)(1.0 / 0.07);
     const int K = P.K;
 
-    // this thread's slice of W0 (rows rb*IQ .. +IQ, column col) and of its gradient accumulator
-    float wreg[WREG ? IQ : 1], w0acc[IQ];
+    // pos / usr warps: this lane's slice of W0 (rows grow*RL .. +RL of column gcol); the two warps hold W0 once
+    const int gcol = (role == 2 ? D / 2 : 0) + lane / LC, grow = lane % LC;
+    float wreg[RL];
+    auto load_w0 = [&]() {
 #pragma unroll
-    for (int i = 0; i < IQ; ++i) w0acc[i] = 0.f;
-    if (WREG) {
-        if (role == 0) {
-#pragma unroll
-            for (int i = 0; i < IQ; ++i) wreg[WREG ? i : 0] = __ldcg(P.w0 + (rb * IQ + i) * D + col);
-        }
-    } else {
-        for (int i = tid * 4; i < D * D; i += NROW * 4) *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
-    }
-
-    // f = mean . W0 (behavior_aggregators.cpp:118): 4 lanes share a column, 16 FMAs each, two shuffles
-    auto gemv = [&](const float *mean_) {
-        const float *pm = mean_ + rb * IQ;
+        for (int i = 0; i < RL; ++i) wreg[i] = __ldcg(P.w0 + (grow * RL + i) * D + gcol);
+    };
+    if (role != 0) load_w0();
+    // f[gcol] = sum_r mean[r] * W0[r][gcol] (behavior_aggregators.cpp:118): D/2 columns per warp
+    auto gemv_half = [&](const float *mean_) {
+        const float *pm = mean_ + grow * RL;
         float f0 = 0.f, f1 = 0.f, f2 = 0.f, f3 = 0.f;
 #pragma unroll
-        for (int i4 = 0; i4 < IQ; i4 += 4) {
+        for (int i4 = 0; i4 < RL; i4 += 4) {
             const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
-            if (WREG) {
-                f0 = fmaf(m4.x, wreg[WREG ? i4 : 0], f0); f1 = fmaf(m4.y, wreg[WREG ? i4 + 1 : 0], f1);
-                f2 = fmaf(m4.z, wreg[WREG ? i4 + 2 : 0], f2); f3 = fmaf(m4.w, wreg[WREG ? i4 + 3 : 0], f3);
-            } else {
-                const float *w = W0s + (rb * IQ + i4) * D + col;
-                f0 = fmaf(m4.x, w[0], f0); f1 = fmaf(m4.y, w[D], f1); f2 = fmaf(m4.z, w[2 * D], f2); f3 = fmaf(m4.w, w[3 * D], f3);
-            }
+            f0 = fmaf(m4.x, wreg[i4], f0); f1 = fmaf(m4.y, wreg[i4 + 1], f1);
+            f2 = fmaf(m4.z, wreg[i4 + 2], f2); f3 = fmaf(m4.w, wreg[i4 + 3], f3);
         }
         float f = (f0 + f1) + (f2 + f3);
-        f += __shfl_xor_sync(FULL, f, 1);
-        f += __shfl_xor_sync(FULL, f, 2);
-        if (rb == 0) f_s[col] = f;
+#pragma unroll
+        for (int o = 1; o < LC; o <<= 1) f += __shfl_xor_sync(FULL, f, o);
+        if (grow == 0) f_s[gcol] = f;
     };
-    // W0 gradient of the sample with history mean `pm_all` and 0.6*g_u `g06` (behavior_aggregators.cpp:131-146);
-    // every 32 samples the accumulated step is applied (W0 -= lr0 * acc / 32) and the thread's copy refreshed
-    auto w0_tail = [&](const float *pm_all, const float *g06, bool flush) {
-        const float *pm = pm_all + rb * IQ;
-        const float gq = g06[col];
+    // neg threads: the W0 step of the last `ns` samples (behavior_aggregators.cpp:131-146) as one batched
+    // rank-ns update from the rings: W0 -= lr0 * (sum_s mean_s^T (0.6 g_s)) / 32.  Thread = column tid>>2, rows (tid&3)*IQ..
+    auto w0_step = [&](unsigned upto, int ns) {
+        const int col = tid >> 2, rb = tid & 3;
+        float acc[IQ];
 #pragma unroll
-        for (int i4 = 0; i4 < IQ; i4 += 4) {
-            const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
-            w0acc[i4 + 0] = fmaf(m4.x, gq, w0acc[i4 + 0]); w0acc[i4 + 1] = fmaf(m4.y, gq, w0acc[i4 + 1]);
-            w0acc[i4 + 2] = fmaf(m4.z, gq, w0acc[i4 + 2]); w0acc[i4 + 3] = fmaf(m4.w, gq, w0acc[i4 + 3]);
-        }
-        if (flush) {
+        for (int i = 0; i < IQ; ++i) acc[i] = 0.f;
+        for (int q = ns; q > 0; --q) {
+            const unsigned sidx = upto - (unsigned)q;
+            const float *pm = mean_ring + (sidx & (MRING - 1)) * D + rb * IQ;
+            const float gq = gu06_ring[(sidx & (GRING - 1)) * D + col];
 #pragma unroll
-            for (int i = 0; i < IQ; ++i) {
-                const int e = (rb * IQ + i) * D + col;
-                const float delta = -(P.lr_w0 * (w0acc[i] / 32.0f));
-                const float old = atomicAdd(P.w0 + e, delta);    // returns the value before: picks up other CTAs' steps
-                if (WREG) wreg[WREG ? i : 0] = old + delta; else W0s[e] = old + delta;
-                w0acc[i] = 0.f;
+            for (int i4 = 0; i4 < IQ; i4 += 4) {
+                const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
+                acc[i4 + 0] = fmaf(m4.x, gq, acc[i4 + 0]); acc[i4 + 1] = fmaf(m4.y, gq, acc[i4 + 1]);
+                acc[i4 + 2] = fmaf(m4.z, gq, acc[i4 + 2]); acc[i4 + 3] = fmaf(m4.w, gq, acc[i4 + 3]);
             }
         }
+#pragma unroll
+        for (int i = 0; i < IQ; ++i) atomicAdd(P.w0 + (rb * IQ + i) * D + col, -(P.lr_w0 * (acc[i] / 32.0f)));
     };
 
     float4 u_keep = f4zero(), gu_keep = f4zero();            // usr: the row / grad row of user keep_u after its last step
@@ -336,8 +337,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     unsigned it = 0;                                         // samples processed by this CTA
     double loss_acc = 0.0;
     float loss_f = 0.f;
-    int mb = 0;                                              // mean buffer of this sample (ring of 3)
-    if (!WREG) row_bar<NROW>();                              // W0s staged
+#ifdef HEAT_CTA_PROFILE
+    const bool prof_on = blockIdx.x == 0 && lane == 0;
+    long long prof_abs[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+#endif
     batch_bar<NT>();                                         // #1
 
     for (int rbuf = 0;; rbuf = rbuf == 2 ? 0 : rbuf + 1) {
@@ -350,13 +353,14 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             const int u = m->u, p = m->p, H = m->H, fl = m->flags;
             const bool fresh = (fl & CTA_FRESH) != 0, dup = (fl & CTA_DUP) != 0;
             const int nfl = mn ? mn->flags : 0, nu = mn ? mn->u : -1;
-            const bool pf = PF && mn != nullptr && !(nfl & CTA_LATE);      // block-uniform
-            float *mean = meanb + mb * D;
-            const float *mean_prev = meanb + (mb == 0 ? 2 : mb - 1) * D;
-            float *mean_next = meanb + (mb == 2 ? 0 : mb + 1) * D;
+            const bool pf = mn != nullptr && !(nfl & CTA_LATE);                  // block-uniform
+            float *mean = mean_ring + (it & (MRING - 1)) * D;
+            float *mean_next = mean_ring + ((it + 1) & (MRING - 1)) * D;
+            HEAT_PT(0);
 
-            // ---- the rows of this sample (prefetched during the previous sample, or loaded now), then the
-            //      prefetch of the next sample's rows
+            // ---- the rows of this sample: prefetched during the previous sample, or loaded now (first sample,
+            //      or a sample sharing an item row with its predecessor: after that one's stores)
+            if (fl & CTA_LATE) row_bar<NROW>();
             int nid[NPS];
             float4 nw[NPS], gn[NPS];
             float4 rw = f4zero(), rg = f4zero();              // positive / user weight and grad slices
@@ -375,18 +379,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         gn[n] = k < K ? ldcg4(P.item_g + (size_t)nid[n] * D + 4 * sl) : f4zero();
                     }
                 }
-                if (pf) {
-#pragma unroll
-                    for (int n = 0; n < NPS; ++n) {
-                        const int k = slot + 16 * n;
-                        nidn[n] = k < K ? mn->negid[k] : 0;
-                        if (k < K) {
-                            cp_async16(stage + (2 * n) * STG, P.item_w + (size_t)nidn[n] * D + 4 * sl);
-                            cp_async16(stage + (2 * n + 1) * STG, P.item_g + (size_t)nidn[n] * D + 4 * sl);
-                        }
-                    }
-                    cp_async_commit();
-                }
             } else if (role == 1) {
                 if (have_pf) {
                     cp_async_wait0();
@@ -394,11 +386,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 } else {
                     rw = ldcg4(P.item_w + (size_t)p * D + 4 * sl);
                     rg = ldcg4(P.item_g + (size_t)p * D + 4 * sl);
-                }
-                if (pf) {
-                    cp_async16(stage, P.item_w + (size_t)mn->p * D + 4 * sl);
-                    cp_async16(stage + STG, P.item_g + (size_t)mn->p * D + 4 * sl);
-                    cp_async_commit();
                 }
             } else {
                 if (u == keep_u) {                             // the run continues: the row is in registers
@@ -411,17 +398,11 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     rg = ldcg4(P.user_g + (size_t)u * D + 4 * sl);
                 }
                 if (!urow_done) *reinterpret_cast<float4 *>(urow_s + 4 * sl) = rw;
-                pf_u = -1;
-                if (pf && nu != u) {                           // the next sample starts another user's run
-                    pf_u = nu;
-                    cp_async16(stage, P.user_w + (size_t)nu * D + 4 * sl);
-                    cp_async16(stage + STG, P.user_g + (size_t)nu * D + 4 * sl);
-                    cp_async_commit();
-                }
             }
-            have_pf = pf;
+            HEAT_PT(1);
             // ---- first sample of a run: gather the history rows (behavior_aggregators.cpp:96-105)
             if (fresh) {
+                row_bar<NROW>();                              // the previous sample's row stores are done
                 const int *hrow = P.his + (size_t)u * P.max_his;
                 float4 a4 = f4zero();
                 for (int h = slot; h < H; h += NSLOT) a4 = a4 + ldcg4(P.item_w + (size_t)__ldg(hrow + h) * D + 4 * sl);
@@ -437,19 +418,51 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 row_bar<NROW>();
             }
             // ---- a W0 step is due (every 32 samples): it must land before this sample's mean.W0
-            const bool flush_due = it > 0 && (it & 31) == 0;
-            if (flush_due) {
-                row_bar<NROW>();                              // the usr warp has published 0.6*g_u of the previous sample
-                if (role == 0) w0_tail(mean_prev, gu06_s + ((it - 1) & 1) * D, true);
+            if (it > 0 && (it & 31) == 0) {
+                row_bar<NROW>();                              // the rings hold the last 32 samples
+                if (role == 0) w0_step(it, 32);
+                row_bar<NROW>();
+                if (role != 0) load_w0();
             }
-            if (role == 0 && !have_f) gemv(mean);
+            if (role != 0 && !have_f) gemv_half(mean);
+            HEAT_PT(2);
             row_bar<NROW>();                                                          // [G1]
+            // ---- prefetch of the next sample's rows (ordered after every store of the previous sample by [G1];
+            //      a row shared with THIS sample makes the next one "late" instead)
+            if (pf) {
+                if (role == 0) {
+#pragma unroll
+                    for (int n = 0; n < NPS; ++n) {
+                        const int k = slot + 16 * n;
+                        nidn[n] = k < K ? mn->negid[k] : 0;
+                        if (k < K) {
+                            cp_async16(stage + (2 * n) * STG, P.item_w + (size_t)nidn[n] * D + 4 * sl);
+                            cp_async16(stage + (2 * n + 1) * STG, P.item_g + (size_t)nidn[n] * D + 4 * sl);
+                        }
+                    }
+                    cp_async_commit();
+                } else if (role == 1) {
+                    cp_async16(stage, P.item_w + (size_t)mn->p * D + 4 * sl);
+                    cp_async16(stage + STG, P.item_g + (size_t)mn->p * D + 4 * sl);
+                    cp_async_commit();
+                }
+            }
+            if (role == 2) {
+                pf_u = -1;
+                if (pf && nu != u) {                           // the next sample starts another user's run
+                    pf_u = nu;
+                    cp_async16(stage, P.user_w + (size_t)nu * D + 4 * sl);
+                    cp_async16(stage + STG, P.user_g + (size_t)nu * D + 4 * sl);
+                    cp_async_commit();
+                }
+            }
+            have_pf = pf;
             // ---- u <- gamma*u + (1-gamma)*f (:122); the slot's dots in one butterfly
             //      (matrix_factorization.cpp:45-53, 82-85); E_k = exp(cos_k / T), published as per-slot sums
             float4 ua = gamma * *reinterpret_cast<const float4 *>(urow_s + 4 * sl);
             fma4(ua, omg, *reinterpret_cast<const float4 *>(f_s + 4 * sl));
             float uu, rinv_u, pp = 0.f, upd = 0.f;
-            float un[NPS], nn[NPS], Ek[NPS], r3[NPS], rn3[NPS];
+            float un[NPS], nn[NPS], Ek[NPS], rn3[NPS];
             if (role == 0) {
                 float r[1 + 2 * NPS];
                 r[0] = dot4(ua, ua);
@@ -459,17 +472,20 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 uu = r[0];
                 rinv_u = rsqrt_eps(uu);
                 float es = 0.f, bs = 0.f;
+                float4 gpart = f4zero();
 #pragma unroll
                 for (int n = 0; n < NPS; ++n) {
                     un[n] = r[1 + 2 * n]; nn[n] = r[2 + 2 * n];
                     const float rinv_n = rsqrt_eps(nn[n]);
                     Ek[n] = (slot + 16 * n < K) ? expf((un[n] * (rinv_u * rinv_n)) * score_mul) : 0.f;
-                    r3[n] = (rinv_u * rinv_u) * (rinv_u * rinv_n);             // 1 / (|u|^3 |n|)   (:136)
+                    const float r3 = (rinv_u * rinv_u) * (rinv_u * rinv_n);    // 1 / (|u|^3 |n|)   (:136)
                     rn3[n] = (rinv_u * rinv_n) * (rinv_n * rinv_n);            // 1 / (|u| |n|^3)   (:137)
                     es += Ek[n];
-                    bs = fmaf(Ek[n], r3[n] * un[n], bs);
+                    bs = fmaf(Ek[n], r3 * un[n], bs);
+                    fma4(gpart, (Ek[n] * r3) * uu, nw[n]);     // the N[k] part of gu_n (:138), still without lg's common factor
                 }
                 if (sl == 0) { sE[slot] = es; sB[slot] = bs; }
+                *reinterpret_cast<float4 *>(part + slot * D + 4 * sl) = gpart;
             } else if (role == 1) {
                 float r[3] = {dot4(ua, ua), dot4(rw, rw), dot4(ua, rw)};
                 group_sum_n<LPR, 3>(r);
@@ -484,9 +500,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 uu = r[0];
                 rinv_u = rsqrt_eps(uu);
             }
+            HEAT_PT(3);
             row_bar<NROW>();                                                          // [A]
             // ---- softmax with the implicit zero logit (matrix_factorization.cpp:55-61, 91-109):
-            //      esum = 1 + sum_k exp((cos_k - cos_p)/T) = 1 + Ep * sum_k E_k;  lg_k = (E_k Ep / esum) / T.
+            //      esum = 1 + sum_k exp((cos_k - cos_p)/T) = 1 + Ep * sum_k E_k;  lg_k = cE * E_k, cE = (Ep / esum) / T.
             //      No max shift: |cos/T| <= 14.3, far inside fp32 range.
             float SE;
             {
@@ -498,22 +515,46 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             const float Ep = sc3[2];
             const float esum = fmaf(Ep, SE, 1.0f);
             const float cE = (Ep * score_mul) / esum;
+            have_f = mn != nullptr && !(nfl & CTA_FRESH) && ((it + 1) & 31) != 0;   // next mean.W0 can be computed now
             float c1[NPS], c2[NPS];
-            float4 gp = f4zero(), gacc = f4zero();
-            if (role == 0) {
-                // lg*gn_n = c1*u + c2*N[k];  the N[k] part of lg*gu_n is c3*N[k] (:138-143)
-                float4 gpart = f4zero();
+            float4 gp = f4zero();
+            if (role == 2) {
+                // ---- user row: grad (:60-62, :141), aggregator backward, step (:152, :166, :171-172).  This is the
+                //      only work between [A] and the next sample's [G1] that the next sample waits for.
+                float4 g0 = f4zero(), g1 = f4zero(), g2 = f4zero(), g3 = f4zero();
 #pragma unroll
-                for (int n = 0; n < NPS; ++n) {
-                    const float lg = cE * Ek[n];               // :109
-                    c1[n] = (lg * rn3[n]) * nn[n];
-                    c2[n] = -(lg * rn3[n]) * un[n];
-                    fma4(gpart, (lg * r3[n]) * uu, nw[n]);
+                for (int q = 0; q < 16; q += 4) {
+                    g0 = g0 + *reinterpret_cast<const float4 *>(part + q * D + 4 * sl);
+                    g1 = g1 + *reinterpret_cast<const float4 *>(part + (q + 1) * D + 4 * sl);
+                    g2 = g2 + *reinterpret_cast<const float4 *>(part + (q + 2) * D + 4 * sl);
+                    g3 = g3 + *reinterpret_cast<const float4 *>(part + (q + 3) * D + 4 * sl);
                 }
-                *reinterpret_cast<float4 *>(part + slot * D + 4 * sl) = gpart;
+                const float4 b0 = *reinterpret_cast<const float4 *>(sB), b1 = *reinterpret_cast<const float4 *>(sB + 4);
+                const float4 b2 = *reinterpret_cast<const float4 *>(sB + 8), b3 = *reinterpret_cast<const float4 *>(sB + 12);
+                const float4 b = (b0 + b1) + (b2 + b3);
+                const float SB = (b.x + b.y) + (b.z + b.w);
+                pp = sc3[0]; upd = sc3[1];
+                const float4 pw = *reinterpret_cast<const float4 *>(pw_s + 4 * sl);
+                const float q3 = (cE * SE) * ((rinv_u * rinv_u) * (rinv_u * rsqrt_eps(pp)));   // lgsum / (|u|^3 |p|)
+                // sum_k lg_k*gu_n_k - lgsum*gu_p;  gu_n = (uu*n - un*u)/(|u|^3|n|),  gu_p = (uu*p - up*u)/(|u|^3|p|)
+                float4 gu = rg;
+                fma4(gu, cE, (g0 + g1) + (g2 + g3));
+                fma4(gu, fmaf(q3, upd, -(cE * SB)), ua);
+                fma4(gu, -q3 * uu, pw);
+                *reinterpret_cast<float4 *>(gu06_ring + (it & (GRING - 1)) * D + 4 * sl) = omg * gu;   // behavior_aggregators.cpp:131-139
+                gu = gamma * gu;                                                                       // :148-152
+                gu = clamp4(gu, P.clip);
+                fma4(ua, -P.lr, gu);
+                urow_done = nu == u;
+                if (urow_done) *reinterpret_cast<float4 *>(urow_s + 4 * sl) = ua;                      // the next sample's input row
+                stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
+                stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
+                u_keep = ua; gu_keep = gu; keep_u = u;
+                mean_wait();                                   // the pos warp has published the next history mean
+                if (have_f) gemv_half(mean_next);
             } else if (role == 1) {
-                // positive row grad (:142), clipped (:169); I[p] moves by -lr*gp: carry that into the cached column
-                // sums and publish the mean of the run's next sample (a gather overwrites both)
+                // ---- positive row grad (:142), clipped (:169); I[p] moves by -lr*gp: carry that into the cached column
+                //      sums and publish the mean of the run's next sample (a gather overwrites both)
                 const float rinv_p = rsqrt_eps(pp);
                 const float q = (cE * SE) * ((rinv_u * rinv_p) * (rinv_p * rinv_p));   // lgsum / (|u| |p|^3)
                 gp = rg;
@@ -523,58 +564,33 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 fma4(a4, (fl & CTA_REGATHER) ? 0.f : -P.lr * (float)m->pmult, gp);
                 *reinterpret_cast<float4 *>(accs + 4 * sl) = a4;
                 *reinterpret_cast<float4 *>(mean_next + 4 * sl) = m->rH * a4;
+                __syncwarp();
+                mean_arrive();
+                if (have_f) gemv_half(mean_next);
             } else {
-                // everything of the user grad that does not need the slots' partial sums (:60-62, :141)
-                const float4 b0 = *reinterpret_cast<const float4 *>(sB), b1 = *reinterpret_cast<const float4 *>(sB + 4);
-                const float4 b2 = *reinterpret_cast<const float4 *>(sB + 8), b3 = *reinterpret_cast<const float4 *>(sB + 12);
-                const float4 b = (b0 + b1) + (b2 + b3);
-                const float SB = (b.x + b.y) + (b.z + b.w);
-                pp = sc3[0]; upd = sc3[1];
-                const float4 pw = *reinterpret_cast<const float4 *>(pw_s + 4 * sl);
-                const float q3 = (cE * SE) * ((rinv_u * rinv_u) * (rinv_u * rsqrt_eps(pp)));   // lgsum / (|u|^3 |p|)
-                // sum_k lg_k*(-un_k/(|u|^3|n_k|))*u  - lgsum*gu_p,  gu_p = (uu*p - up*u)/(|u|^3|p|)
-                gacc = rg;
-                fma4(gacc, fmaf(q3, upd, -(cE * SB)), ua);
-                fma4(gacc, -q3 * uu, pw);
-            }
-            row_bar<NROW>();                                                          // [B]
-            // ---- after [B]: nothing below is on the next sample's critical path except the usr warp's step
-            if (role == 2) {
-                // user row: sum of the slots' partial grads, aggregator backward, step (:141, :152, :166, :171-172)
-                float4 g0 = f4zero(), g1 = f4zero(), g2 = f4zero(), g3 = f4zero();
-#pragma unroll
-                for (int q = 0; q < 16; q += 4) {
-                    g0 = g0 + *reinterpret_cast<const float4 *>(part + q * D + 4 * sl);
-                    g1 = g1 + *reinterpret_cast<const float4 *>(part + (q + 1) * D + 4 * sl);
-                    g2 = g2 + *reinterpret_cast<const float4 *>(part + (q + 2) * D + 4 * sl);
-                    g3 = g3 + *reinterpret_cast<const float4 *>(part + (q + 3) * D + 4 * sl);
-                }
-                float4 gu = gacc + ((g0 + g1) + (g2 + g3));
-                *reinterpret_cast<float4 *>(gu06_s + (it & 1) * D + 4 * sl) = omg * gu;   // behavior_aggregators.cpp:131-139
-                gu = gamma * gu;                                                          // :148-152
-                gu = clamp4(gu, P.clip);
-                fma4(ua, -P.lr, gu);
-                urow_done = nu == u;
-                if (urow_done) *reinterpret_cast<float4 *>(urow_s + 4 * sl) = ua;         // the next sample's input row
-                stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
-                stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
-                u_keep = ua; gu_keep = gu; keep_u = u;
-            }
-            // ---- negative rows: clipped step, write-back (:127-150; sgd.cpp:14-26)
-            if (role == 0 && !dup) {
+                // ---- negative rows: lg*gn_n = c1*u + c2*N[k] (:139-143), clipped step, write-back (:127-150; sgd.cpp:14-26)
 #pragma unroll
                 for (int n = 0; n < NPS; ++n) {
-                    if (slot + 16 * n < K) {
-                        float4 gk = gn[n];
-                        fma4(gk, c1[n], ua); fma4(gk, c2[n], nw[n]);
-                        gk = clamp4(gk, P.clip);
-                        float4 wk = nw[n];
-                        fma4(wk, -P.lr, gk);
-                        stcg4(P.item_w + (size_t)nid[n] * D + 4 * sl, wk);   // :148
-                        stcg4(P.item_g + (size_t)nid[n] * D + 4 * sl, gk);   // :149
+                    const float lg = cE * Ek[n];               // :109
+                    c1[n] = (lg * rn3[n]) * nn[n];
+                    c2[n] = -(lg * rn3[n]) * un[n];
+                }
+                if (!dup) {
+#pragma unroll
+                    for (int n = 0; n < NPS; ++n) {
+                        if (slot + 16 * n < K) {
+                            float4 gk = gn[n];
+                            fma4(gk, c1[n], ua); fma4(gk, c2[n], nw[n]);
+                            gk = clamp4(gk, P.clip);
+                            float4 wk = nw[n];
+                            fma4(wk, -P.lr, gk);
+                            stcg4(P.item_w + (size_t)nid[n] * D + 4 * sl, wk);   // :148
+                            stcg4(P.item_g + (size_t)nid[n] * D + 4 * sl, gk);   // :149
+                        }
                     }
                 }
             }
+            HEAT_PT(4);
             if (dup) {
                 // duplicate ids: replay in the reference's k order (grad row re-read per k, last writer
                 // wins on the weight row); the positive row is written after all negatives (:169-174)
@@ -610,21 +626,23 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     if (P.loss_out) P.loss_out[m->s - P.begin] = loss;
                 }
             }
-            // ---- W0 outer product of the PREVIOUS sample; mean.W0 of the NEXT one when nothing can change its inputs
-            have_f = mn != nullptr && !(nfl & CTA_FRESH) && ((it + 1) & 31) != 0;
-            if (role == 0) {
-                if (it > 0 && !flush_due) w0_tail(mean_prev, gu06_s + ((it - 1) & 1) * D, false);
-                if (have_f) gemv(mean_next);
-            }
+            HEAT_PT(5);
+#ifdef HEAT_CTA_PROFILE
+            if (prof_on && it == 1000)
+                printf("abs tid %3d fresh %d: top %lld rows %lld G1 %lld A %lld S %lld end %lld\n", tid, (int)fresh,
+                       prof_abs[0] % 1000000, prof_abs[1] % 1000000, prof_abs[2] % 1000000, prof_abs[3] % 1000000,
+                       prof_abs[4] % 1000000, prof_abs[5] % 1000000);
+#endif
             it += 1;
-            mb = (mb == 2) ? 0 : mb + 1;
         }
         batch_bar<NT>();                                     // this batch is consumed; the batch after the next is visible
     }
-    // ---- W0 gradient of the last sample and the leftover (< 32 samples) accumulators
+    // ---- W0 step of the leftover (<= 32) samples (the reference drops a partial batch of W0 grads: drop_w0_tail)
     row_bar<NROW>();
-    if (it > 0 && role == 0)
-        w0_tail(meanb + (mb == 0 ? 2 : mb - 1) * D, gu06_s + ((it - 1) & 1) * D, ((it & 31) == 0) || !P.drop_w0_tail);
+    {
+        const int left = (it & 31) == 0 ? (it > 0 ? 32 : 0) : (P.drop_w0_tail ? 0 : (int)(it & 31));
+        if (left > 0 && role == 0) w0_step(it, left);
+    }
     if (role == 1 && lane == 0) {
         loss_acc += (double)loss_f;
         if (loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);

@@ -46,8 +46,6 @@ int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
     if (D == 64 && K <= 16) return launch_cta<64, 1>(c, P, blocks);
     if (D == 64 && K <= 32) return launch_cta<64, 2>(c, P, blocks);
     if (D == 64 && K <= 64) return launch_cta<64, 4>(c, P, blocks);
-    if (D == 128 && K <= 16) return launch_cta<128, 1>(c, P, blocks);
-    if (D == 128 && K <= 64) return launch_cta<128, 4>(c, P, blocks);
     if (D == 32 && K <= 16) return launch_cta<32, 1>(c, P, blocks);
     if (D == 32 && K <= 32) return launch_cta<32, 2>(c, P, blocks);
     return -1;
