@@ -8,21 +8,23 @@
 // critical path.  Warp roles (every warp is role-uniform):
 //
 //   neg warps   16 slots of D/4 lanes; slot q owns the negative rows k = q, q+16, ... (NPS per slot).
-//               The same 4D threads compute mean.W0 against a REGISTER-resident slice of W0 (D <= 64)
-//               and own the matching slice of the W0 gradient accumulator.
-//   pos warp    the positive row, the loss, the patch of the cached history column sums.
+//               The same 4D threads hold W0 in REGISTERS (D/4 rows of one column each), compute mean.W0 and
+//               apply the batched W0 step every 32 samples from shared-memory rings of (mean, 0.6 g_u).
+//   pos warp    the positive row, the loss, the patch of the cached history column sums -> next history mean.
 //   usr warp    the user row, kept in registers across a user's run.
 //   ctl warp    runs ahead on its own loop: one LANE per sample, 32 samples per batch -- click, Philox
 //               negatives, duplicate / conflict detection, history membership -- into a ring of three
 //               batches; it meets the row warps once per batch (named barrier 2).
 //
-// Per sample the row warps meet at three named barriers; between them sits only what the next stage needs:
-//   [B]  usr: finish the user step (sum of the slots' partial grads), publish the next u
-//        neg: row steps + stores, W0 outer product of the previous sample, mean.W0 of the NEXT sample
-//        all: this sample's rows were prefetched (cp.async) during the previous sample; issue the next prefetch
-//   [G1] all: u <- 0.4u + 0.6f, the slot's dots in one interleaved butterfly, E_k = exp(cos_k/T)
-//   [A]  all: esum = 1 + exp(-cos_p/T) * sum_k E_k from 16 shared partials; neg: partial user grads;
-//        pos: its clipped step, the next sample's history mean
+// Per sample the row warps meet at two full barriers; between them sits only what the next stage needs:
+//   [G1] all: issue the cp.async prefetch of the NEXT sample's rows; u <- 0.4u + 0.6f; the slot's dots in one
+//        interleaved butterfly; E_k = exp(cos_k/T) and the UNNORMALISED partial user grads, published per slot
+//   [A]  all: esum = 1 + exp(-cos_p/T) * sum_k E_k from 16 shared partials (no cross-slot shuffles);
+//        usr: user grad, aggregator backward, clipped step, next sample's input row     (the critical chain)
+//        pos: clipped step, patched column sums, next history mean -> named barrier 3 -> neg: mean.W0 of the next sample
+//        neg: clipped row steps, stores
+//   Rows come from the prefetch slots; a sample sharing an item row with its predecessor ("late") or starting
+//   a run ("fresh": history gather) loads after an extra barrier, behind the predecessor's stores.
 // Same arithmetic as train_kernel.cuh (reference: models/matrix_factorization.cpp:15-181,
 // behavior_aggregators/behavior_aggregators.cpp:51-153, optimizers/sgd.cpp:14-26) up to fp32 rounding:
 // 1/sqrt as MUFU.RSQ + one Newton step, softmax as exp(a)*exp(-b) instead of exp(a-b-max).  With one CTA
@@ -47,16 +49,14 @@ template <int NPS> struct CtaBatch {
 };
 
 template <int D, int NPS> struct CtaCfg {
-    static_assert(D == 32 || D == 64, "the CTA engine covers emb_dim 32 and 64 (W0 halves live in the pos / usr warps' registers)");
+    static_assert(D == 32 || D == 64, "the CTA engine covers emb_dim 32 and 64");
     static constexpr int LPR = D / 4;                       // lanes per row
     static constexpr int NEGT = 16 * LPR;                    // threads of the negative slots (whole warps)
     static constexpr int POS0 = NEGT, USR0 = POS0 + 32, CTRL0 = USR0 + 32;
     static constexpr int NT = CTRL0 + 32;
     static constexpr int NSLOT = 18;
     static constexpr int KMAX = 16 * NPS;
-    static constexpr int IQ = D / 4;                         // W0 rows per thread in the batched W0 step (neg threads)
-    static constexpr int LC = 64 / D;                        // GEMV: lanes per column (pos / usr warp, D/2 columns each)
-    static constexpr int RL = D / LC;                        // GEMV: W0 rows per lane
+    static constexpr int IQ = D / 4;                         // W0 rows per neg thread (GEMV and the batched W0 step)
     static constexpr int MRING = 64, GRING = 32;             // history means of the last 64 samples, 0.6*g_u of the last 32
     // shared memory, in floats
     static constexpr int OFF_MEAN = 0;                       // [MRING][D]
@@ -74,11 +74,11 @@ template <int D, int NPS> struct CtaCfg {
 };
 
 // named barriers: 1 = the row warps, 2 = row warps + control warp (once per batch),
-// 3 = pos warp (arrives: the next history mean is published) + usr warp (waits for it)
+// 3 = pos warp (arrives: the next history mean is published) + neg warps (wait for it)
 template <int N> __device__ __forceinline__ void row_bar() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
 template <int N> __device__ __forceinline__ void batch_bar() { asm volatile("bar.sync 2, %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void mean_arrive() { asm volatile("bar.arrive 3, 64;" ::: "memory"); }
-__device__ __forceinline__ void mean_wait() { asm volatile("bar.sync 3, 64;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void mean_arrive() { asm volatile("bar.arrive 3, %0;" ::"n"(N) : "memory"); }
+template <int N> __device__ __forceinline__ void mean_wait() { asm volatile("bar.sync 3, %0;" ::"n"(N) : "memory"); }
 
 // N independent sums over the VL lanes of a row group in ONE butterfly: the N shuffles of a step are
 // issued back to back, so the latency of a step is paid once, not N times.
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
 {
     using C = CtaCfg<D, NPS>;
     constexpr int LPR = C::LPR, NSLOT = C::NSLOT, IQ = C::IQ, NROW = C::CTRL0, NT = C::NT;
-    constexpr int LC = C::LC, RL = C::RL, MRING = C::MRING, GRING = C::GRING;
+    constexpr int MRING = C::MRING, GRING = C::GRING;
     extern __shared__ __align__(16) float smem[];
     float *mean_ring = smem + C::OFF_MEAN, *gu06_ring = smem + C::OFF_GU06, *accs = smem + C::OFF_ACC, *f_s = smem + C::OFF_F;
     float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW;
@@ -283,33 +283,31 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     const float score_mul = (float)(1.0 / 0.07);
     const int K = P.K;
 
-    // pos / usr warps: this lane's slice of W0 (rows grow*RL .. +RL of column gcol); the two warps hold W0 once
-    const int gcol = (role == 2 ? D / 2 : 0) + lane / LC, grow = lane % LC;
-    float wreg[RL];
-    auto load_w0 = [&]() {
+    // neg threads: slice of W0 (rows rb*IQ .. +IQ of column col) in registers; 4 lanes share a column
+    const int col = tid >> 2, rb = tid & 3;
+    float wreg[IQ];
+    if (role == 0) {
 #pragma unroll
-        for (int i = 0; i < RL; ++i) wreg[i] = __ldcg(P.w0 + (grow * RL + i) * D + gcol);
-    };
-    if (role != 0) load_w0();
-    // f[gcol] = sum_r mean[r] * W0[r][gcol] (behavior_aggregators.cpp:118): D/2 columns per warp
-    auto gemv_half = [&](const float *mean_) {
-        const float *pm = mean_ + grow * RL;
+        for (int i = 0; i < IQ; ++i) wreg[i] = __ldcg(P.w0 + (rb * IQ + i) * D + col);
+    }
+    // f = mean . W0 (behavior_aggregators.cpp:118): IQ FMAs per thread, two shuffles
+    auto gemv = [&](const float *mean_) {
+        const float *pm = mean_ + rb * IQ;
         float f0 = 0.f, f1 = 0.f, f2 = 0.f, f3 = 0.f;
 #pragma unroll
-        for (int i4 = 0; i4 < RL; i4 += 4) {
+        for (int i4 = 0; i4 < IQ; i4 += 4) {
             const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
             f0 = fmaf(m4.x, wreg[i4], f0); f1 = fmaf(m4.y, wreg[i4 + 1], f1);
             f2 = fmaf(m4.z, wreg[i4 + 2], f2); f3 = fmaf(m4.w, wreg[i4 + 3], f3);
         }
         float f = (f0 + f1) + (f2 + f3);
-#pragma unroll
-        for (int o = 1; o < LC; o <<= 1) f += __shfl_xor_sync(FULL, f, o);
-        if (grow == 0) f_s[gcol] = f;
+        f += __shfl_xor_sync(FULL, f, 1);
+        f += __shfl_xor_sync(FULL, f, 2);
+        if (rb == 0) f_s[col] = f;
     };
     // neg threads: the W0 step of the last `ns` samples (behavior_aggregators.cpp:131-146) as one batched
-    // rank-ns update from the rings: W0 -= lr0 * (sum_s mean_s^T (0.6 g_s)) / 32.  Thread = column tid>>2, rows (tid&3)*IQ..
+    // rank-ns update from the rings: W0 -= lr0 * (sum_s mean_s^T (0.6 g_s)) / 32; the thread's slice is refreshed
     auto w0_step = [&](unsigned upto, int ns) {
-        const int col = tid >> 2, rb = tid & 3;
         float acc[IQ];
 #pragma unroll
         for (int i = 0; i < IQ; ++i) acc[i] = 0.f;
@@ -325,7 +323,11 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             }
         }
 #pragma unroll
-        for (int i = 0; i < IQ; ++i) atomicAdd(P.w0 + (rb * IQ + i) * D + col, -(P.lr_w0 * (acc[i] / 32.0f)));
+        for (int i = 0; i < IQ; ++i) {
+            const float delta = -(P.lr_w0 * (acc[i] / 32.0f));
+            const float old = atomicAdd(P.w0 + (rb * IQ + i) * D + col, delta);   // returns the value before: picks up other CTAs' steps
+            wreg[i] = old + delta;
+        }
     };
 
     float4 u_keep = f4zero(), gu_keep = f4zero();            // usr: the row / grad row of user keep_u after its last step
@@ -405,7 +407,16 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 row_bar<NROW>();                              // the previous sample's row stores are done
                 const int *hrow = P.his + (size_t)u * P.max_his;
                 float4 a4 = f4zero();
-                for (int h = slot; h < H; h += NSLOT) a4 = a4 + ldcg4(P.item_w + (size_t)__ldg(hrow + h) * D + 4 * sl);
+                for (int h0 = slot; h0 < H; h0 += 8 * NSLOT) {   // 8 ids, then 8 rows in flight per thread
+                    int hid[8];
+                    float4 hr[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) hid[q] = (h0 + q * NSLOT < H) ? __ldg(hrow + h0 + q * NSLOT) : -1;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) hr[q] = hid[q] >= 0 ? ldcg4(P.item_w + (size_t)hid[q] * D + 4 * sl) : f4zero();
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) a4 = a4 + hr[q];
+                }
                 *reinterpret_cast<float4 *>(hpart + slot * D + 4 * sl) = a4;
                 row_bar<NROW>();
                 if (tid < D) {
@@ -421,10 +432,8 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             if (it > 0 && (it & 31) == 0) {
                 row_bar<NROW>();                              // the rings hold the last 32 samples
                 if (role == 0) w0_step(it, 32);
-                row_bar<NROW>();
-                if (role != 0) load_w0();
             }
-            if (role != 0 && !have_f) gemv_half(mean);
+            if (role == 0 && !have_f) gemv(mean);
             HEAT_PT(2);
             row_bar<NROW>();                                                          // [G1]
             // ---- prefetch of the next sample's rows (ordered after every store of the previous sample by [G1];
@@ -457,6 +466,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 }
             }
             have_pf = pf;
+            HEAT_PT(9);
             // ---- u <- gamma*u + (1-gamma)*f (:122); the slot's dots in one butterfly
             //      (matrix_factorization.cpp:45-53, 82-85); E_k = exp(cos_k / T), published as per-slot sums
             float4 ua = gamma * *reinterpret_cast<const float4 *>(urow_s + 4 * sl);
@@ -470,6 +480,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 for (int n = 0; n < NPS; ++n) { r[1 + 2 * n] = dot4(ua, nw[n]); r[2 + 2 * n] = dot4(nw[n], nw[n]); }
                 group_sum_n<LPR, 1 + 2 * NPS>(r);
                 uu = r[0];
+                HEAT_PT(10);
                 rinv_u = rsqrt_eps(uu);
                 float es = 0.f, bs = 0.f;
                 float4 gpart = f4zero();
@@ -518,6 +529,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             have_f = mn != nullptr && !(nfl & CTA_FRESH) && ((it + 1) & 31) != 0;   // next mean.W0 can be computed now
             float c1[NPS], c2[NPS];
             float4 gp = f4zero();
+            HEAT_PT(6);
             if (role == 2) {
                 // ---- user row: grad (:60-62, :141), aggregator backward, step (:152, :166, :171-172).  This is the
                 //      only work between [A] and the next sample's [G1] that the next sample waits for.
@@ -550,8 +562,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
                 stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
                 u_keep = ua; gu_keep = gu; keep_u = u;
-                mean_wait();                                   // the pos warp has published the next history mean
-                if (have_f) gemv_half(mean_next);
             } else if (role == 1) {
                 // ---- positive row grad (:142), clipped (:169); I[p] moves by -lr*gp: carry that into the cached column
                 //      sums and publish the mean of the run's next sample (a gather overwrites both)
@@ -565,8 +575,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 *reinterpret_cast<float4 *>(accs + 4 * sl) = a4;
                 *reinterpret_cast<float4 *>(mean_next + 4 * sl) = m->rH * a4;
                 __syncwarp();
-                mean_arrive();
-                if (have_f) gemv_half(mean_next);
+                mean_arrive<C::NEGT + 32>();
             } else {
                 // ---- negative rows: lg*gn_n = c1*u + c2*N[k] (:139-143), clipped step, write-back (:127-150; sgd.cpp:14-26)
 #pragma unroll
@@ -589,6 +598,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         }
                     }
                 }
+                HEAT_PT(7);
+                mean_wait<C::NEGT + 32>();                     // the pos warp has published the next history mean
+                HEAT_PT(8);
+                if (have_f) gemv(mean_next);                   // mean.W0 of the next sample, off its critical path
             }
             HEAT_PT(4);
             if (dup) {
@@ -629,9 +642,9 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             HEAT_PT(5);
 #ifdef HEAT_CTA_PROFILE
             if (prof_on && it == 1000)
-                printf("abs tid %3d fresh %d: top %lld rows %lld G1 %lld A %lld S %lld end %lld\n", tid, (int)fresh,
-                       prof_abs[0] % 1000000, prof_abs[1] % 1000000, prof_abs[2] % 1000000, prof_abs[3] % 1000000,
-                       prof_abs[4] % 1000000, prof_abs[5] % 1000000);
+                printf("abs tid %3d fresh %d: top %lld rows %lld G1 %lld pfi %lld bfly %lld A %lld cE %lld st %lld mw %lld S %lld end %lld\n", tid, (int)fresh,
+                       prof_abs[0] % 1000000, prof_abs[1] % 1000000, prof_abs[2] % 1000000, prof_abs[9] % 1000000, prof_abs[10] % 1000000, prof_abs[3] % 1000000,
+                       prof_abs[6] % 1000000, prof_abs[7] % 1000000, prof_abs[8] % 1000000, prof_abs[4] % 1000000, prof_abs[5] % 1000000);
 #endif
             it += 1;
         }
