@@ -198,7 +198,7 @@ def run_gpu_arm(args, rank, world, local_rank):
 
     ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=1.0, l_r=1e-2, milestones=(10,), seed=2022,
                       sample_offset=rank * N, device=local_rank, update_mode=args.update_mode,
-                      warps_per_block=args.warps, max_blocks=args.max_blocks, chunk=args.chunk)
+                      warps_per_block=args.warps, max_blocks=args.max_blocks, chunk=args.chunk, engine=args.engine)
     ctx.set_dataset(clicks, his, masks)
     ctx.bind_tables(uw, iw, w0)
     if world > 1:
@@ -269,6 +269,41 @@ def run_gpu_arm(args, rank, world, local_rank):
     e2e_s = reduce_max(time.perf_counter() - t0)
     e2e_value = world * N * e2e_steps / e2e_s
     ctx.close()
+
+    # ---- throughput mode, reported beside the headline: the warp-per-sample kernel on a full grid (thousands of
+    #      samples in flight).  Faster, but its Hogwild dynamics leave the reference's Recall@20,
+    #      so it is not the configuration `value` is quoted on.
+    thr = None
+    if args.engine == 0 and not args.no_throughput_mode:
+        for t, t0_ in zip((uw, iw, w0), init):
+            t[...] = t0_
+        ctx2 = abi.Context(D, K, d.num_users, d.num_items, clip_val=1.0, l_r=1e-2, milestones=(10,), seed=2022,
+                           sample_offset=rank * N, device=local_rank, engine=1)
+        ctx2.set_dataset(clicks, his, masks)
+        ctx2.bind_tables(uw, iw, w0)
+        if world > 1:
+            uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                uid.copy_(torch.from_numpy(abi.Context.comm_unique_id()))
+            dist.broadcast(uid, 0)
+            ctx2.comm_init(rank, world, uid.cpu().numpy())
+            ctx2.set_sync_interval(args.sync_interval)
+        for _ in range(args.warmup):
+            flush_l2(); ctx2.train_epoch()
+        barrier()
+        ms2, k2 = [], []
+        for _ in range(args.steps):
+            flush_l2(); ctx2.train_epoch()
+            ms2.append(ctx2.last_epoch_ms()); k2.append(ctx2.last_kernel_ms())
+        barrier()
+        tot2 = reduce_max(float(np.sum(ms2)))
+        thr = {"value": world * N * args.steps / (tot2 * 1e-3), "unit": UNIT, "ms_per_step": tot2 / args.steps,
+               "kernel": "heat::train_kernel (warp per sample, full grid)", "kernel_ms": float(np.mean(k2)),
+               "recall_parity": "outside the 0.005 tolerance (profiles/r01_recall_parity.md)"}
+        ctx2.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
 
@@ -280,7 +315,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     table_bytes = 2 * (d.num_users + d.num_items) * D * 4
     l2_peak = abi.probe_l2_bandwidth(local_rank, table_bytes, 200)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": args.ncu_traffic, "peak_source": peak_src, "kernel": "heat::train_kernel",
+                "traffic": args.ncu_traffic, "peak_source": peak_src,
+                "kernel": "heat::train_cta_kernel" if args.engine != 1 else "heat::train_kernel",
                 "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                 "note": "weights+grads (%.0f MB) are L2-resident: the bound that applies is the L2 row "
                         "gather/scatter rate, measured by heat_probe_l2_bandwidth on the same footprint" % (table_bytes / 1e6),
@@ -294,7 +330,12 @@ def run_gpu_arm(args, rank, world, local_rank):
                     "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "what": "heat_set_dataset + heat_upload_tables + heat_train_epoch + heat_sync_to_host from pinned host buffers"},
             "roofline": roofline, "loss_first_last": [losses[0], losses[-1]], "wall_s_timed_region": wall,
-            "update_mode": args.update_mode, "sync_interval": args.sync_interval if world > 1 else None}
+            "update_mode": args.update_mode, "sync_interval": args.sync_interval if world > 1 else None,
+            "engine": {0: "auto: CTA-per-sample kernel, parity-grade concurrency", 1: "warp-per-sample kernel, full grid",
+                       2: "CTA-per-sample kernel"}[args.engine]}
+    if thr is not None:
+        thr["l2_frac"] = alg / (thr["kernel_ms"] * 1e-3) / 1e9 / l2_peak
+        line["throughput_mode"] = thr
     if not args.no_cpu_baseline:
         d0, t0_ = (d, init)
         line["cpu_baseline"] = cpu_baseline(d0, t0_, args.cpu_seconds)
@@ -312,6 +353,8 @@ def main():
     ap.add_argument("--warps", type=int, default=0)
     ap.add_argument("--max-blocks", type=int, default=0)
     ap.add_argument("--chunk", type=int, default=0)
+    ap.add_argument("--engine", type=int, default=0, help="0 auto (CTA-per-sample kernel at parity-grade concurrency), 1 warp-per-sample, 2 CTA-per-sample")
+    ap.add_argument("--no-throughput-mode", action="store_true", help="skip the extra warp-per-sample full-grid measurement")
     ap.add_argument("--sync-interval", type=int, default=0, help="samples per GPU between item-delta all-reduces (0 = per epoch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)

@@ -7,7 +7,7 @@ Same YAML keys and epoch / evaluation schedule.  Differences, all on the GPU-pat
   * evaluation runs fused on the GPU (Engine.evaluate_metrics) and honours the YAML `metrics`
     list; `--dense-eval` takes the reference's route (evaluate0 + numpy metrics) instead;
   * optional `gpu:` section of the YAML (seed, update_mode, max_blocks, warps_per_block,
-    sync_interval, sync_average); absent = defaults.
+    sync_interval, sync_average, history_mode, engine); absent = defaults.
 """
 import argparse
 import os

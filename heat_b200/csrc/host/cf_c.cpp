@@ -47,7 +47,9 @@ PYBIND11_MODULE(cf_c, cf_module)
         .def_readwrite("update_mode", &CFConfig::update_mode)
         .def_readwrite("warps_per_block", &CFConfig::warps_per_block)
         .def_readwrite("max_blocks", &CFConfig::max_blocks)
-        .def_readwrite("sync_average", &CFConfig::sync_average);
+        .def_readwrite("sync_average", &CFConfig::sync_average)
+        .def_readwrite("history_mode", &CFConfig::history_mode)
+        .def_readwrite("engine", &CFConfig::engine);
 
     py::module_ datasets = m.def_submodule("datasets", "datasets");
     py::class_<Dataset, std::shared_ptr<Dataset>>(datasets, "Dataset");

@@ -66,7 +66,10 @@ typedef struct heat_config {
     uint32_t engine;            /* 0 auto; 1 warp-per-sample kernel (train_kernel.cuh: highest throughput, thousands of
                                    samples in flight); 2 CTA-per-sample kernel (train_kernel_cta.cuh: lowest latency per
                                    sample, one sample in flight per thread block -- the default where it applies) */
-    uint32_t max_blocks;        /* 0 = one grid over all SMs; else cap on thread blocks (bounds Hogwild concurrency) */
+    uint32_t max_blocks;        /* cap on thread blocks = bound on Hogwild concurrency.  0 = default: with engine 0 the
+                                   CTA kernel runs min(#SMs, max(8, num_items/600)) blocks (one sample in flight per
+                                   ~600 item rows keeps Recall@20 on the reference's); engines
+                                   1 and 2 use one grid over all SMs */
 } heat_config;
 
 /* ---- life cycle -------------------------------------------------------------------- */

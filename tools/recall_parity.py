@@ -38,7 +38,9 @@ out["reference"] = {"losses": ref_losses, "sec_per_epoch": ref_s, "threads": o.m
 print("reference", [round(x, 4) for x in ref_losses], {k: round(v, 4) for k, v in ref_res.items()}, f"{ref_s:.2f} s/epoch", flush=True)
 for mode in modes:
     t = synth.init_tables(d.num_users, d.num_items, D)
-    if mode.startswith("cta"):            # cta:<max_blocks>:<blocks_per_sm>
+    if mode == "auto":                    # library defaults: CTA kernel, blocks = min(#SMs, num_items/600)
+        ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip)
+    elif mode.startswith("cta"):          # cta:<max_blocks>:<blocks_per_sm>
         _, mb, bps = mode.split(":")
         ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=2, max_blocks=int(mb), blocks_per_sm=int(bps))
     else:                                 # <warps>:<max_blocks>:<update_mode>  (warp-per-sample engine)
