@@ -41,6 +41,24 @@ def algorithmic_bytes(clicks, masks, d=D, k=K):
     return float(np.sum(4 * d * (4 * (2 + k) + h) + 12 + 4 * h))
 
 
+def ncu_traffic(kernel_file):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed ncu --set full capture."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", kernel_file)
+    try:
+        import csv
+        with open(path) as f:
+            rows = list(csv.reader(f))
+        head, unit, val = rows[0], rows[1], rows[2]
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot = 0.0
+        for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = head.index(k)
+            tot += float(val[i].replace(",", "")) * scale[unit[i]]
+        return tot
+    except Exception:
+        return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -315,7 +333,9 @@ def run_gpu_arm(args, rank, world, local_rank):
     table_bytes = 2 * (d.num_users + d.num_items) * D * 4
     l2_peak = abi.probe_l2_bandwidth(local_rank, table_bytes, 200)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": args.ncu_traffic, "peak_source": peak_src,
+                "traffic": args.ncu_traffic if args.ncu_traffic is not None else ncu_traffic(
+                    "r01_train_cta_kernel_ncu_raw.csv" if args.engine != 1 else "r01_train_kernel_ncu_raw.csv"),
+                "traffic_source": "profiles/ ncu --set full capture of the same bench command (bytes per launch)", "peak_source": peak_src,
                 "kernel": "heat::train_cta_kernel" if args.engine != 1 else "heat::train_kernel",
                 "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                 "note": "weights+grads (%.0f MB) are L2-resident: the bound that applies is the L2 row "
