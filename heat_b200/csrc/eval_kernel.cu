@@ -69,6 +69,66 @@ struct EvalSmem {
     static size_t bytes(int stages, int k) { return 1024 + A_BYTES + (size_t)stages * B_STAGE + (size_t)k * EV_M * 8 + BAR_BYTES; }
 };
 
+// Top-k entries are 64-bit keys: order-preserving bits of the score in the high word, (0x7fffffff - item id) in the
+// low word, so ONE unsigned compare orders by score and, among equal scores, puts the smaller id first.
+__device__ __forceinline__ unsigned long long topk_key(float s, int id)
+{
+    unsigned u = __float_as_uint(s);
+    u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    return ((unsigned long long)u << 32) | (unsigned)(0x7fffffff - id);
+}
+__device__ __forceinline__ float topk_key_score(unsigned long long key)
+{
+    unsigned u = (unsigned)(key >> 32);
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    return __uint_as_float(u);
+}
+__device__ __forceinline__ int topk_key_id(unsigned long long key) { return 0x7fffffff - (int)(unsigned)key; }
+
+// One candidate of row `row`: skip it if it is a train item of the user (metrics.py:21-24; the lists are sorted and
+// columns arrive in increasing order, so one forward-only cursor `tp` serves the whole row), else put it into the row's
+// top-k set (column-major in shared memory).  The set is UNSORTED while the columns stream by: a new member
+// overwrites the current minimum and the minimum is found again by one unrolled pass over k keys (independent
+// loads) instead of shifting half of a sorted list through shared memory; topk_sort orders it once at the end.
+__device__ __noinline__ void topk_insert(const int *__restrict__ train_items, long long &tp, long long te, unsigned long long *list,
+                                         int row, int k, int &cnt, float &thr, int &minpos, float s, int col)
+{
+    while (tp < te && __ldg(train_items + tp) < col) ++tp;
+    if (tp < te && __ldg(train_items + tp) == col) return;
+    const unsigned long long key = topk_key(s, col);
+    if (cnt < k) {
+        list[cnt * EV_M + row] = key;
+        if (++cnt < k) return;
+    } else {
+        list[minpos * EV_M + row] = key;
+    }
+    unsigned long long best = list[row];
+    int bj = 0;
+#pragma unroll 10
+    for (int j = 1; j < k; ++j) {
+        const unsigned long long v = list[j * EV_M + row];
+        if (v < best) { best = v; bj = j; }
+    }
+    thr = topk_key_score(best); minpos = bj;
+}
+
+// Descending keys: insertion sort of the row's `cnt` entries (every row of the block sorts at the same time,
+// once per user block).
+__device__ __noinline__ void topk_sort(unsigned long long *list, int row, int cnt)
+{
+    for (int a = 1; a < cnt; ++a) {
+        const unsigned long long key = list[a * EV_M + row];
+        int pos = a;
+        while (pos > 0) {
+            const unsigned long long pk = list[(pos - 1) * EV_M + row];
+            if (pk > key) break;
+            list[pos * EV_M + row] = pk;
+            --pos;
+        }
+        list[pos * EV_M + row] = key;
+    }
+}
+
 template <int D, int NT>
 __global__ void __launch_bounds__(EV_THREADS, 1)
 eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
@@ -83,9 +143,8 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t *sA = smem;                                       // [hi|lo][KA][128 x 128B]
     uint8_t *sB = sA + S::A_BYTES;                            // [stage][hi|lo][KA][NT x 128B]
-    float *list_s = reinterpret_cast<float *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [k][128]
-    int *list_i = reinterpret_cast<int *>(list_s + (size_t)P.k * EV_M);                 // [k][128]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(list_i) + (size_t)P.k * EV_M * 4);
+    unsigned long long *list = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [k][128] keys
+    uint64_t *bars = reinterpret_cast<uint64_t *>(list + (size_t)P.k * EV_M);
     uint64_t *full = bars, *empty = bars + MAX_B_STAGES;
     uint64_t *tfull = bars + 2 * MAX_B_STAGES, *tempty = tfull + ACC_STAGES;
     uint64_t *a_full = tempty + ACC_STAGES, *a_empty = a_full + 1;
@@ -175,7 +234,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x) {
             const int u = rb * EV_M + row;
             const bool row_ok = u < P.U;
-            int cnt = 0;
+            int cnt = 0, minpos = 0;
             float thr = -INFINITY;
             long long tp = 0, te = 0;
             if (row_ok && P.train_indptr) { tp = P.train_indptr[u]; te = P.train_indptr[u + 1]; }
@@ -201,30 +260,19 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                 }
 #pragma unroll
                 for (int i = 0; i < NT; ++i) {
+                    // the test is all the unrolled loop holds; the rare survivor goes through ONE out-of-line copy of the
+                    // mask check + insertion (64 inlined copies thrashed the instruction cache: profiles/r01_eval_*)
                     const float s = v[i];
-                    const int col = col0 + i;
                     const bool cand = (cnt < k) ? (s == s) : (s > thr);
-                    if (cand && col < P.I) {
-                        // train-item mask (metrics.py:21-24): lists are sorted and columns arrive in
-                        // increasing order, so one forward-only cursor serves the whole row
-                        while (tp < te && __ldg(P.train_items + tp) < col) ++tp;
-                        if (tp < te && __ldg(P.train_items + tp) == col) continue;
-                        int pos = (cnt < k) ? cnt++ : k - 1;
-                        while (pos > 0 && list_s[(pos - 1) * EV_M + row] < s) {      // ties keep the smaller id first
-                            list_s[pos * EV_M + row] = list_s[(pos - 1) * EV_M + row];
-                            list_i[pos * EV_M + row] = list_i[(pos - 1) * EV_M + row];
-                            --pos;
-                        }
-                        list_s[pos * EV_M + row] = s;
-                        list_i[pos * EV_M + row] = col;
-                        if (cnt == k) thr = list_s[(k - 1) * EV_M + row];
-                    }
+                    if (cand && col0 + i < P.I) topk_insert(P.train_items, tp, te, list, row, k, cnt, thr, minpos, s, col0 + i);
                 }
             }
             if (row_ok && k > 0) {
+                topk_sort(list, row, cnt);
                 for (int j = 0; j < k; ++j) {
-                    P.topk_ids[(size_t)u * k + j] = j < cnt ? list_i[j * EV_M + row] : -1;
-                    if (P.topk_scores) P.topk_scores[(size_t)u * k + j] = j < cnt ? list_s[j * EV_M + row] : -INFINITY;
+                    const unsigned long long key = j < cnt ? list[j * EV_M + row] : 0ull;
+                    P.topk_ids[(size_t)u * k + j] = j < cnt ? topk_key_id(key) : -1;
+                    if (P.topk_scores) P.topk_scores[(size_t)u * k + j] = j < cnt ? topk_key_score(key) : -INFINITY;
                 }
             }
         }
