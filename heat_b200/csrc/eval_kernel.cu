@@ -258,13 +258,19 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                         if (col0 + i < P.I) out[i] = v[i];
                     continue;
                 }
+                // the unrolled loop holds one max-of-4 test per four scores; the rare survivors go through ONE out-of-line
+                // copy of the mask check + insertion (64 inlined copies thrashed the instruction cache: profiles/r01_eval_*)
 #pragma unroll
-                for (int i = 0; i < NT; ++i) {
-                    // the test is all the unrolled loop holds; the rare survivor goes through ONE out-of-line copy of the
-                    // mask check + insertion (64 inlined copies thrashed the instruction cache: profiles/r01_eval_*)
-                    const float s = v[i];
-                    const bool cand = (cnt < k) ? (s == s) : (s > thr);
-                    if (cand && col0 + i < P.I) topk_insert(P.train_items, tp, te, list, row, k, cnt, thr, minpos, s, col0 + i);
+                for (int i = 0; i < NT; i += 4) {
+                    const float m4 = fmaxf(fmaxf(v[i], v[i + 1]), fmaxf(v[i + 2], v[i + 3]));
+                    if (m4 > thr || cnt < k) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float s = v[i + e];
+                            const bool cand = (cnt < k) ? (s == s) : (s > thr);
+                            if (cand && col0 + i + e < P.I) topk_insert(P.train_items, tp, te, list, row, k, cnt, thr, minpos, s, col0 + i + e);
+                        }
+                    }
                 }
             }
             if (row_ok && k > 0) {
