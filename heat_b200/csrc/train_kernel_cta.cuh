@@ -178,7 +178,9 @@ __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch
     bool conf = false, dup = false;
     const CtaMeta<NPS> *prev = lane > 0 ? &B->meta[lane - 1] : c.prev_last;
     const bool has_prev = act && prev != nullptr;
-    const int prev_p = has_prev ? prev->p : -8000;
+    int prev_p = __shfl_up_sync(FULL, p, 1);               // lane-1's positive (its meta fields are written at the end)
+    if (lane == 0) prev_p = c.prev_last ? c.prev_last->p : -8000;
+    if (!has_prev) prev_p = -8000;
 #pragma unroll 4
     for (int b = 0; b < K; ++b) {
         const int vm = act ? my->negid[b] : -8100, vp = has_prev ? prev->negid[b] : -8200;
