@@ -58,6 +58,9 @@ int fail(const std::string &msg);
 
 // train_launch.cu
 int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host);
+// train_bigk.cu
+struct TrainParams;
+int dispatch_bigk(Ctx *c, const TrainParams &P, bool deterministic);
 // eval_kernel.cu
 int eval_dense(Ctx *c, float *out_host);
 int eval_topk(Ctx *c, uint32_t k, const int64_t *train_indptr, const int32_t *train_items,

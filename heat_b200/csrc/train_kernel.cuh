@@ -42,6 +42,7 @@ struct TrainParams {
     int max_his, num_items, K, chunk, drop_w0_tail;
     int upd;                 // item-row update mode, see UPD_* below
     int no_cache;            // 1: gather the history rows for every sample (history_mode 1)
+    int cache_rows;          // train_kernel_bigk.cuh: negative rows kept in shared memory between the two passes
     float lr, lr_w0, clip;
 };
 

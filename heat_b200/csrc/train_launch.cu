@@ -37,6 +37,9 @@ int launch_cta(Ctx *c, const TrainParams &P, int blocks)
     return 0;
 }
 
+// does the warp-per-sample kernel have an instantiation for (D, K)?
+bool warp_covers(int D, int K) { return (D == 64 && K <= 32) || (D == 128 && K <= 16) || (D == 32 && K <= 32); }
+
 // CTA-per-sample engine (train_kernel_cta.cuh): returns -1 when (D, K) is outside what it covers.
 int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
 {
@@ -104,7 +107,7 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic)
 #undef HEAT_LAUNCH_UPD
 #undef HEAT_LAUNCH
     return fail("unsupported (emb_dim, num_negs) = (" + std::to_string(D) + ", " + std::to_string(K) +
-                "): the register-resident kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16");
+                "): the warp-per-sample kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16 (engine 0 or 3 covers the rest)");
 }
 
 }  // namespace
@@ -138,9 +141,13 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
 
     P.no_cache = c->cfg.history_mode == 1;
     int rc = -1;
-    if (c->cfg.engine != 1) rc = dispatch_cta(c, P, c->cfg.deterministic != 0);      // 0 auto, 2 forced
+    if (c->cfg.engine != 1 && c->cfg.engine != 3) rc = dispatch_cta(c, P, c->cfg.deterministic != 0);      // 0 auto, 2 forced
     if (rc == -1 && c->cfg.engine == 2) rc = fail("engine 2 (CTA per sample) does not cover this (emb_dim, num_negs)");
-    if (rc == -1) rc = dispatch(c, P, c->cfg.deterministic != 0);
+    if (rc == -1) {
+        const bool det = c->cfg.deterministic != 0;
+        if (c->cfg.engine == 3 || (c->cfg.engine == 0 && !warp_covers((int)c->cfg.emb_dim, P.K))) rc = dispatch_bigk(c, P, det);
+        else rc = dispatch(c, P, det);
+    }
     if (rc == 0) {
         double loss = 0.0;
         cudaError_t e = cudaMemcpyAsync(&loss, c->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);

@@ -5,6 +5,8 @@ import numpy as np
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TRAIN_CASES = ["train_d64_k16", "train_d128_k16", "train_d64_k16_dups", "train_d32_k8"]
+# large-negative regime (train_kernel_bigk.cuh); their `negs` table holds the first 72 samples only
+BIGK_CASES = ["train_d128_k1000", "train_d64_k200", "train_d32_k48"]
 
 
 def load_golden(name):

@@ -5,7 +5,7 @@ import pytest
 
 import oracle
 from heat_b200 import synth
-from helpers import TRAIN_CASES, fresh_tables, load_golden, rel_err
+from helpers import BIGK_CASES, TRAIN_CASES, fresh_tables, load_golden, rel_err
 
 
 def test_philox_known_answers():
@@ -16,16 +16,16 @@ def test_philox_known_answers():
                                 [0xa4093822, 0x299f31d0]) == [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
 
 
-@pytest.mark.parametrize("name", TRAIN_CASES)
+@pytest.mark.parametrize("name", TRAIN_CASES + BIGK_CASES)
 def test_neg_table_matches_golden_and_rules(name):
     g = load_golden(name)
     K, I = int(g["K"]), g["init_item_w"].shape[0]
     negs = oracle.neg_table(int(g["seed"]), 0, 0, g["clicks"], K, I)
-    assert np.array_equal(negs, g["negs"])
+    assert np.array_equal(negs[:g["negs"].shape[0]], g["negs"])
     assert negs.max() < I
     # look-back rule == the reference's persistent vector (uniform_random_negative_sampler.cpp:26-36)
     persistent = np.zeros(K, np.uint64)
-    for s in range(min(300, g["clicks"].shape[0])):
+    for s in range(min(300 if K <= 16 else 12, g["clicks"].shape[0])):
         for k in range(K):
             c = [s & 0xffffffff, s >> 32, 0, k >> 2]
             r = oracle.philox4x32_10(c, [int(g["seed"]) & 0xffffffff, int(g["seed"]) >> 32])[k & 3]
@@ -35,7 +35,7 @@ def test_neg_table_matches_golden_and_rules(name):
         assert np.array_equal(persistent, negs[s]), s
 
 
-@pytest.mark.parametrize("name", TRAIN_CASES)
+@pytest.mark.parametrize("name", TRAIN_CASES + BIGK_CASES)
 @pytest.mark.parametrize("steps", [1, 3])
 def test_c_oracle_matches_reference_golden(name, steps):
     g = load_golden(name)

@@ -4,7 +4,7 @@ import pytest
 
 import oracle
 from heat_b200 import abi, synth
-from helpers import TRAIN_CASES, fresh_tables, load_golden, rel_err
+from helpers import BIGK_CASES, TRAIN_CASES, fresh_tables, load_golden, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -17,7 +17,7 @@ def make_ctx(g, **kw):
     return ctx
 
 
-@pytest.mark.parametrize("name", TRAIN_CASES)
+@pytest.mark.parametrize("name", TRAIN_CASES + BIGK_CASES)
 @pytest.mark.parametrize("epoch,offset", [(0, 0), (3, 0), (1, 123456789012)])
 def test_sampler_bit_exact(name, epoch, offset):
     g = load_golden(name)
@@ -28,7 +28,7 @@ def test_sampler_bit_exact(name, epoch, offset):
     ref = oracle.neg_table(int(g["seed"]), epoch, offset, g["clicks"], int(g["K"]), I)
     assert np.array_equal(dev, ref)
     if epoch == 0 and offset == 0:
-        assert np.array_equal(dev, g["negs"])
+        assert np.array_equal(dev[:g["negs"].shape[0]], g["negs"])
     part = ctx.sample_negatives(epoch, 17, 101)
     assert np.array_equal(part, ref[17:101])
 
@@ -47,12 +47,17 @@ def test_history_gather_indices_bit_exact(name):
     assert np.array_equal(ids, want)
 
 
-@pytest.mark.parametrize("name", TRAIN_CASES)
+# engine 0 = the default for the shape (large num_negs -> train_kernel_bigk.cuh); engine 3 forces the
+# large-negative kernel onto the small shapes too
+ENGINE_CASES = [(n, 0) for n in TRAIN_CASES + BIGK_CASES] + [(n, 3) for n in TRAIN_CASES]
+
+
+@pytest.mark.parametrize("name,engine", ENGINE_CASES)
 @pytest.mark.parametrize("steps", [1, 3])
-def test_steps_match_reference_golden(name, steps):
+def test_steps_match_reference_golden(name, engine, steps):
     g = load_golden(name)
     uw, iw, w0 = fresh_tables(g)
-    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1)
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1, engine=engine)
     ctx.bind_tables(uw, iw, w0)
     total, per = ctx.train_range(0, steps, per_sample=True)
     ctx.sync_to_host()
@@ -66,14 +71,14 @@ def test_steps_match_reference_golden(name, steps):
         assert rel_err(got, g[t + key]) < lim, (key, rel_err(got, g[t + key]))
 
 
-@pytest.mark.parametrize("name", TRAIN_CASES)
-def test_each_sample_alone_matches_oracle(name):
+@pytest.mark.parametrize("name,engine", ENGINE_CASES)
+def test_each_sample_alone_matches_oracle(name, engine):
     """Teacher-forced: every one of the first 64 samples, applied alone to the SAME initial state,
     must match the oracle's single step (covers duplicate negatives, draws equal to the positive,
     short and full histories)."""
     g = load_golden(name)
     D, K = int(g["D"]), int(g["K"])
-    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1)
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1, engine=engine)
     uw, iw, w0 = fresh_tables(g)
     ctx.bind_tables(uw, iw, w0)
     worst = 0.0
@@ -93,14 +98,15 @@ def test_each_sample_alone_matches_oracle(name):
     print(name, "worst single-step rel err", worst)
 
 
-@pytest.mark.parametrize("name", ["train_d64_k16", "train_d128_k16", "train_d32_k8"])
-def test_w0_update_with_frozen_tables(name):
+@pytest.mark.parametrize("name,engine", [("train_d64_k16", 0), ("train_d128_k16", 0), ("train_d32_k8", 0), ("train_d64_k16", 3),
+                                         ("train_d128_k16", 3), ("train_d128_k1000", 0), ("train_d64_k200", 0), ("train_d32_k48", 0)])
+def test_w0_update_with_frozen_tables(name, engine):
     """70 sequential samples with the table LR at 0: two W0 updates (iterations 32 and 64), the tail
     dropped as the reference does; nothing chaotic, so the whole state must agree."""
     g = load_golden(name)
     D, K = int(g["D"]), int(g["K"])
     uw, iw, w0 = fresh_tables(g)
-    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1)
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1, engine=engine)
     ctx.bind_tables(uw, iw, w0)
     ctx.set_lr(0.0)
     _, per = ctx.train_range(0, 70, per_sample=True)

@@ -26,11 +26,13 @@ OUT = os.path.join(ROOT, "tests", "golden")
 SEED = 2022
 
 
-def train_case(name, U, I, N, D, K, H, clip, lr, steps_at=(1, 3, 40)):
+def train_case(name, U, I, N, D, K, H, clip, lr, steps_at=(1, 3, 40), negs_keep=None):
     d = synth.generate(U, I, N, max_his=H, seed=SEED, n_clusters=4, max_degree=I // 2)
     uw, iw, w0 = synth.init_tables(U, I, D, seed=SEED)
     init = dict(user_w=uw.copy(), item_w=iw.copy(), w0=w0.copy())
     negs = oracle.neg_table(SEED, 0, 0, d.clicks, K, I)
+    if negs_keep is not None:          # large num_negs: keep the table small (tests use the first rows only)
+        negs = negs[:negs_keep].copy()
     ref = oracle.RefOracle(D, K, d.clicks, d.his_items, d.masks, uw, iw, w0, clip_val=clip, l_r=lr)
     out = dict(clicks=d.clicks, his_items=d.his_items, masks=d.masks, negs=negs,
                D=D, K=K, clip=np.float32(clip), lr=np.float32(lr), seed=SEED, **{"init_" + k: v for k, v in init.items()})
@@ -86,4 +88,9 @@ if __name__ == "__main__":
     train_case("train_d128_k16", U=48, I=80, N=1200, D=128, K=16, H=100, clip=0.1, lr=1e-2)
     train_case("train_d64_k16_dups", U=64, I=24, N=600, D=64, K=16, H=20, clip=1.0, lr=1e-2)
     train_case("train_d32_k8", U=40, I=64, N=800, D=32, K=8, H=50, clip=1.0, lr=1e-2)
+    # the large-negative regime (BASELINE.json configs[3] is emb_dim 128, num_negs 1000); I=1000 makes every
+    # sample carry many duplicate negatives, the other two have few
+    train_case("train_d128_k1000", U=16, I=1000, N=300, D=128, K=1000, H=100, clip=1.0, lr=1e-2, steps_at=(1, 3), negs_keep=72)
+    train_case("train_d64_k200", U=32, I=2000, N=400, D=64, K=200, H=50, clip=1.0, lr=1e-2, steps_at=(1, 3), negs_keep=72)
+    train_case("train_d32_k48", U=32, I=500, N=400, D=32, K=48, H=50, clip=0.1, lr=1e-2, steps_at=(1, 3), negs_keep=72)
     eval_case("eval_d64", U=96, I=400, N=3000, D=64, H=100)
