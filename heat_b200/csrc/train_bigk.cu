@@ -12,7 +12,7 @@ int launch_bigk(Ctx *c, TrainParams P, int blocks)
 {
     using C = BigKCfg<D>;
     auto kern = train_bigk_kernel<D>;
-    const BigKLayout L = bigk_layout(D, C::G, P.K);
+    const BigKLayout L = bigk_layout(D, C::G, P.K, C::RING);
     const int max_smem = 232448;                              // 227 KB: the per-block opt-in limit of sm_100
     if (L.off_cache > max_smem) return fail("num_negs too large for the large-negative kernel's shared-memory tables");
     P.cache_rows = std::min(P.K, (max_smem - L.off_cache) / (D * 4));
