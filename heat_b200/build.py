@@ -34,6 +34,21 @@ def _deps(directory):
     return out
 
 
+def _includes(path, seen=None):
+    """The file and every quoted #include it reaches (per-object dependency list)."""
+    seen = set() if seen is None else seen
+    path = os.path.normpath(path)
+    if path in seen or not os.path.exists(path):
+        return seen
+    seen.add(path)
+    with open(path) as f:
+        for line in f:
+            line = line.strip()
+            if line.startswith('#include "'):
+                _includes(os.path.join(os.path.dirname(path), line.split('"')[1]), seen)
+    return seen
+
+
 def build_cuda(force=False, verbose=False):
     if not force and not _newer(LIB, _deps(CSRC)):
         return LIB
@@ -43,6 +58,9 @@ def build_cuda(force=False, verbose=False):
     for src in CUDA_SOURCES:
         obj = os.path.join(HERE, "build", src + ".o")
         objs.append(obj)
+        if not force and not verbose and not os.environ.get("HEAT_NVCC_DEFS") and \
+                not _newer(obj, list(_includes(os.path.join(CSRC, src)))):
+            continue
         cmd = ["nvcc", *NVCC_FLAGS, *os.environ.get("HEAT_NVCC_DEFS", "").split(), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

@@ -15,9 +15,10 @@
 //   warp 0      TMA producer   A (users, hi+lo) once per block; B (items, hi+lo) ring of stages
 //   warp 1      MMA issuer     one elected thread, 3 x D/8 tcgen05.mma.kind::tf32 per item tile,
 //                              accumulators double/quad-buffered in TMEM; owns TMEM alloc/dealloc
-//   warps 2..5  epilogue       tcgen05.ld: thread = user row, NT consecutive item scores; threshold
-//                              filter -> (rare) train-mask check + insertion into the row's
-//                              sorted top-k list in shared memory
+//   warps 2..5  epilogue       tcgen05.ld: thread = user row, NT consecutive item scores; a max-of-16
+//                              threshold vote per group, survivors appended to the row's candidate
+//                              buffer in shared memory; a full buffer is folded into the row's sorted
+//                              list by the whole warp (train-mask binary search + bitonic sort)
 #include <algorithm>
 #include <cmath>
 #include <vector>
@@ -42,6 +43,8 @@ struct EvalParams {
     int *topk_ids;                 // [U, k]
     float *topk_scores;            // [U, k]
     float *dense_out;              // [U, I] when k == 0
+    unsigned long long *glist;     // [grid, 128, 32*sort_e - CAP] sorted lists of the user block in flight (L2-resident scratch)
+    int sort_e;                    // keys per lane in the compaction sort: 4, 8 or 16
 };
 
 // x -> hi = tf32(x) (round to nearest, low 13 mantissa bits zero), lo = tf32(x - hi)
@@ -66,7 +69,8 @@ struct EvalSmem {
     static constexpr int A_BYTES = 2 * KA * A_ATOM;         // hi + lo
     static constexpr int B_STAGE = 2 * KA * B_ATOM;         // hi + lo
     static constexpr int BAR_BYTES = 256;
-    static size_t bytes(int stages, int k) { return 1024 + A_BYTES + (size_t)stages * B_STAGE + (size_t)k * EV_M * 8 + BAR_BYTES; }
+    static constexpr int CAP = NT >= 64 ? 64 : 32;          // candidate-buffer entries per user row
+    static size_t bytes(int stages, int k) { return 1024 + A_BYTES + (size_t)stages * B_STAGE + (k ? (size_t)CAP * EV_M * 8 : 0) + BAR_BYTES; }
 };
 
 // Top-k entries are 64-bit keys: order-preserving bits of the score in the high word, (0x7fffffff - item id) in the
@@ -85,48 +89,127 @@ __device__ __forceinline__ float topk_key_score(unsigned long long key)
 }
 __device__ __forceinline__ int topk_key_id(unsigned long long key) { return 0x7fffffff - (int)(unsigned)key; }
 
-// One candidate of row `row`: skip it if it is a train item of the user (metrics.py:21-24; the lists are sorted and
-// columns arrive in increasing order, so one forward-only cursor `tp` serves the whole row), else put it into the row's
-// top-k set (column-major in shared memory).  The set is UNSORTED while the columns stream by: a new member
-// overwrites the current minimum and the minimum is found again by one unrolled pass over k keys (independent
-// loads) instead of shifting half of a sorted list through shared memory; topk_sort orders it once at the end.
-__device__ __noinline__ void topk_insert(const int *__restrict__ train_items, long long &tp, long long te, unsigned long long *list,
-                                         int row, int k, int &cnt, float &thr, int &minpos, float s, int col)
+// Bitonic sort, descending, of 32*E keys held E per lane in blocked order (element index = lane*E + i).
+template <int E>
+__device__ __forceinline__ void bitonic_sort_desc(unsigned long long (&key)[E], int lane)
 {
-    while (tp < te && __ldg(train_items + tp) < col) ++tp;
-    if (tp < te && __ldg(train_items + tp) == col) return;
-    const unsigned long long key = topk_key(s, col);
-    if (cnt < k) {
-        list[cnt * EV_M + row] = key;
-        if (++cnt < k) return;
-    } else {
-        list[minpos * EV_M + row] = key;
+#pragma unroll
+    for (int size = 2; size <= 32 * E; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            if (stride >= E) {
+                const int lmask = stride / E;
+                const bool keep_max = (((lane * E) & size) == 0) == ((lane & lmask) == 0);
+#pragma unroll
+                for (int i = 0; i < E; ++i) {
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[i], lmask);
+                    const bool take = keep_max ? (o > key[i]) : (o < key[i]);
+                    key[i] = take ? o : key[i];
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < E; ++i) {
+                    if ((i & stride) == 0) {
+                        const int j = i | stride;
+                        const bool desc = (((lane * E + i) & size) == 0);
+                        const unsigned long long a = key[i], b = key[j];
+                        const bool sw = desc ? (b > a) : (b < a);
+                        key[i] = sw ? b : a;
+                        key[j] = sw ? a : b;
+                    }
+                }
+            }
+        }
     }
-    unsigned long long best = list[row];
-    int bj = 0;
-#pragma unroll 10
-    for (int j = 1; j < k; ++j) {
-        const unsigned long long v = list[j * EV_M + row];
-        if (v < best) { best = v; bj = j; }
-    }
-    thr = topk_key_score(best); minpos = bj;
 }
 
-// Descending keys: insertion sort of the row's `cnt` entries (every row of the block sorts at the same time,
-// once per user block).
-__device__ __noinline__ void topk_sort(unsigned long long *list, int row, int cnt)
+// Per-lane (= per user row) state of the streaming top-k.  While the item tiles stream by, a lane only APPENDS the
+// scores that beat its row's threshold to the row's candidate buffer (one shared-memory store); the threshold is
+// the k-th best score as of the row's last compaction, so it lags -- that only admits a few extra candidates.
+struct RowState {
+    float thr;          // k-th best unmasked score at the last compaction (valid when full)
+    bool full;          // the row's list holds k unmasked items
+    bool has_list;      // the row's list in global scratch has been written for this user block
+    int cnt;            // candidates waiting in the buffer
+    long long tb, te;   // the user's train items [tb, te), sorted ascending (the -inf mask of metrics.py:21-24)
+};
+
+// Fold the candidate buffers of the rows in `rows` (bit r = row of lane r) into their sorted lists; the whole warp
+// works on one row at a time: the candidates that are train items of the user are dropped (binary search in the
+// user's sorted list -- deferred to here so that the streaming path never touches the CSR), list + candidates are
+// sorted as 32*E keys, the best LCAP = 32*E - CAP go back to the row's list (global scratch, L2-resident) and the
+// k-th one becomes the row's new threshold.  With `final` the first k entries are written out instead.
+template <int E, int CAP>
+__device__ __noinline__ void topk_compact(unsigned rows, RowState &st, int lane, int q, const unsigned long long *buf,
+                                          unsigned long long *glist, const int *__restrict__ train_items, int k, bool final,
+                                          int u_base, int *__restrict__ out_ids, float *__restrict__ out_scores)
 {
-    for (int a = 1; a < cnt; ++a) {
-        const unsigned long long key = list[a * EV_M + row];
-        int pos = a;
-        while (pos > 0) {
-            const unsigned long long pk = list[(pos - 1) * EV_M + row];
-            if (pk > key) break;
-            list[pos * EV_M + row] = pk;
-            --pos;
+    constexpr int LCAP = 32 * E - CAP, LE = LCAP / 32, CE = CAP / 32;
+    const unsigned has = __ballot_sync(0xffffffffu, st.has_list);
+    while (rows) {
+        const int r = __ffs(rows) - 1;
+        rows &= rows - 1;
+        const int row = q * 32 + r;
+        const int n = __shfl_sync(0xffffffffu, st.cnt, r);
+        const long long tb = __shfl_sync(0xffffffffu, st.tb, r), te = __shfl_sync(0xffffffffu, st.te, r);
+        unsigned long long key[E];
+        unsigned long long *gl = glist + (size_t)row * LCAP;
+#pragma unroll
+        for (int i = 0; i < LE; ++i) key[i] = ((has >> r) & 1u) ? __ldcg(gl + lane + 32 * i) : 0ull;
+#pragma unroll
+        for (int i = 0; i < CE; ++i) {
+            const int j = lane + 32 * i;
+            unsigned long long c = j < n ? buf[j * EV_M + row] : 0ull;
+            if (c != 0ull && tb < te) {
+                const int col = 0x7fffffff - (int)(unsigned)c;
+                long long lo = tb, hi = te;
+                while (lo < hi) {
+                    const long long mid = (lo + hi) >> 1;
+                    if (__ldg(train_items + mid) < col) lo = mid + 1; else hi = mid;
+                }
+                if (lo < te && __ldg(train_items + lo) == col) c = 0ull;
+            }
+            key[LE + i] = c;
         }
-        list[pos * EV_M + row] = key;
+        bitonic_sort_desc<E>(key, lane);
+        // k-th best: element index k-1 = lane (k-1)/E, register (k-1)%E
+        unsigned long long kth = 0ull;
+#pragma unroll
+        for (int i = 0; i < E; ++i) kth = ((k - 1) % E == i) ? key[i] : kth;
+        kth = __shfl_sync(0xffffffffu, kth, (k - 1) / E);
+        if (final) {
+            const int u = u_base + row;
+#pragma unroll
+            for (int i = 0; i < E; ++i) {
+                const int j = lane * E + i;
+                if (j < k) {
+                    out_ids[(size_t)u * k + j] = key[i] ? topk_key_id(key[i]) : -1;
+                    if (out_scores) out_scores[(size_t)u * k + j] = key[i] ? topk_key_score(key[i]) : -INFINITY;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < E; ++i) {
+                const int j = lane * E + i;
+                if (j < LCAP) __stcg(gl + j, key[i]);
+            }
+        }
+        if (lane == r) {
+            st.cnt = 0; st.has_list = true;
+            if (kth != 0ull) { st.thr = topk_key_score(kth); st.full = true; }
+        }
     }
+    __syncwarp();
+}
+
+template <int CAP>
+__device__ __forceinline__ void topk_compact_any(int E, unsigned rows, RowState &st, int lane, int q, const unsigned long long *buf,
+                                                 unsigned long long *glist, const int *train_items, int k, bool final, int u_base,
+                                                 int *out_ids, float *out_scores)
+{
+    if (E == 4) topk_compact<4, CAP>(rows, st, lane, q, buf, glist, train_items, k, final, u_base, out_ids, out_scores);
+    else if (E == 8) topk_compact<8, CAP>(rows, st, lane, q, buf, glist, train_items, k, final, u_base, out_ids, out_scores);
+    else topk_compact<16, CAP>(rows, st, lane, q, buf, glist, train_items, k, final, u_base, out_ids, out_scores);
 }
 
 template <int D, int NT>
@@ -143,8 +226,8 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t *sA = smem;                                       // [hi|lo][KA][128 x 128B]
     uint8_t *sB = sA + S::A_BYTES;                            // [stage][hi|lo][KA][NT x 128B]
-    unsigned long long *list = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [k][128] keys
-    uint64_t *bars = reinterpret_cast<uint64_t *>(list + (size_t)P.k * EV_M);
+    unsigned long long *buf = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [CAP][128] candidate keys
+    uint64_t *bars = reinterpret_cast<uint64_t *>(buf + (P.k ? (size_t)S::CAP * EV_M : 0));
     uint64_t *full = bars, *empty = bars + MAX_B_STAGES;
     uint64_t *tfull = bars + 2 * MAX_B_STAGES, *tempty = tfull + ACC_STAGES;
     uint64_t *a_full = tempty + ACC_STAGES, *a_empty = a_full + 1;
@@ -227,17 +310,19 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         }
     } else {
         // ================= epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =================
+        constexpr int CAP = S::CAP;
         const int q = warp & 3;
         const int row = q * 32 + lane;
-        const int k = P.k;
+        const int k = P.k, E = P.sort_e;
+        unsigned long long *glist = P.glist + (size_t)blockIdx.x * EV_M * (32 * E - CAP);
+        unsigned long long *my = buf + row;
         uint32_t it_acc = 0;
         for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x) {
             const int u = rb * EV_M + row;
             const bool row_ok = u < P.U;
-            int cnt = 0, minpos = 0;
-            float thr = -INFINITY;
-            long long tp = 0, te = 0;
-            if (row_ok && P.train_indptr) { tp = P.train_indptr[u]; te = P.train_indptr[u + 1]; }
+            RowState st;
+            st.thr = row_ok ? -INFINITY : INFINITY; st.full = !row_ok; st.has_list = false; st.cnt = 0; st.tb = 0; st.te = 0;
+            if (row_ok && P.train_indptr) { st.tb = P.train_indptr[u]; st.te = P.train_indptr[u + 1]; }
             for (int t = 0; t < P.n_item_tiles; ++t, ++it_acc) {
                 const int acc = it_acc % ACC_STAGES;
                 ptx::mbar_wait(&tfull[acc], (it_acc / ACC_STAGES) & 1);
@@ -250,36 +335,44 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&tempty[acc]);     // accumulator drained into registers
                 const int col0 = t * NT;
-                if (!row_ok) continue;
                 if (k == 0) {
+                    if (!row_ok) continue;
                     float *out = P.dense_out + (size_t)u * P.I + col0;
 #pragma unroll
                     for (int i = 0; i < NT; ++i)
                         if (col0 + i < P.I) out[i] = v[i];
                     continue;
                 }
-                // the unrolled loop holds one max-of-4 test per four scores; the rare survivors go through ONE out-of-line
-                // copy of the mask check + insertion (64 inlined copies thrashed the instruction cache: profiles/r01_eval_*)
+                if (col0 + NT > P.I) {                              // ragged last tile: the padding columns never qualify
 #pragma unroll
-                for (int i = 0; i < NT; i += 4) {
-                    const float m4 = fmaxf(fmaxf(v[i], v[i + 1]), fmaxf(v[i + 2], v[i + 3]));
-                    if (m4 > thr || cnt < k) {
+                    for (int i = 0; i < NT; ++i)
+                        if (col0 + i >= P.I) v[i] = __int_as_float(0x7fc00000);
+                }
+                // Streaming path: ONE warp vote per 16 scores (max-of-16 against the row thresholds).  Only when some
+                // row of the warp has a survivor do the lanes test their 16 scores and append the survivors.
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float s = v[i + e];
-                            const bool cand = (cnt < k) ? (s == s) : (s > thr);
-                            if (cand && col0 + i + e < P.I) topk_insert(P.train_items, tp, te, list, row, k, cnt, thr, minpos, s, col0 + i + e);
-                        }
+                for (int g = 0; g < NT; g += 16) {
+                    float m = v[g];
+#pragma unroll
+                    for (int e = 1; e < 16; ++e) m = fmaxf(m, v[g + e]);
+                    if (!__any_sync(0xffffffffu, !st.full || m > st.thr)) continue;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        const float sc = v[g + e];
+                        const bool cand = st.full ? (sc > st.thr) : (sc == sc);
+                        if (cand) { my[st.cnt * EV_M] = topk_key(sc, col0 + g + e); ++st.cnt; }
+                    }
+                    const unsigned over = __ballot_sync(0xffffffffu, st.cnt > CAP - 16);
+                    if (over) {
+                        __syncwarp();
+                        topk_compact_any<CAP>(E, over, st, lane, q, buf, glist, P.train_items, k, false, 0, nullptr, nullptr);
                     }
                 }
             }
-            if (row_ok && k > 0) {
-                topk_sort(list, row, cnt);
-                for (int j = 0; j < k; ++j) {
-                    const unsigned long long key = j < cnt ? list[j * EV_M + row] : 0ull;
-                    P.topk_ids[(size_t)u * k + j] = j < cnt ? topk_key_id(key) : -1;
-                    if (P.topk_scores) P.topk_scores[(size_t)u * k + j] = j < cnt ? topk_key_score(key) : -INFINITY;
-                }
+            if (k > 0) {
+                const unsigned rows = __ballot_sync(0xffffffffu, row_ok);
+                __syncwarp();
+                topk_compact_any<CAP>(E, rows, st, lane, q, buf, glist, P.train_items, k, true, rb * EV_M, P.topk_ids, P.topk_scores);
             }
         }
     }
@@ -373,6 +466,7 @@ struct EvalScratch {
     long long *test_indptr = nullptr; int *test_items = nullptr; size_t test_n = 0;
     double *sums = nullptr;
     float *dense = nullptr; size_t dense_elems = 0;
+    unsigned long long *glist = nullptr; size_t glist_elems = 0;
 };
 
 template <class T> int ensure(T **p, size_t *have, size_t need)
@@ -430,6 +524,17 @@ int launch_eval(Ctx *c, EvalScratch *s, uint64_t u_begin, uint64_t u_count, Eval
     const size_t smem = S::bytes(stages, P.k);
     HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = std::min(P.n_row_blocks, c->num_sms);
+    if (P.k > 0) {
+        // compaction sort width: 32*E keys >= k + CAP, E in {4, 8, 16}; the lists of the user blocks in flight
+        int E = 4;
+        while (32 * E < P.k + S::CAP) E *= 2;
+        if (E > 16) return fail("evaluation kernel: top-k size too large");
+        P.sort_e = E;
+        size_t have = s->glist_elems;
+        if (int rc = ensure(&s->glist, &have, (size_t)grid * EV_M * (32 * E - S::CAP))) return rc;
+        s->glist_elems = have;
+        P.glist = s->glist;
+    }
     kern<<<grid, EV_THREADS, smem, c->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, P);
     c->launches += 1;
     HEAT_CUDA(cudaGetLastError());
@@ -568,7 +673,7 @@ void eval_free(Ctx *c)
     if (!s) return;
     cudaFree(s->user_hi); cudaFree(s->user_lo); cudaFree(s->item_hi); cudaFree(s->item_lo);
     cudaFree(s->topk_ids); cudaFree(s->topk_scores); cudaFree(s->train_indptr); cudaFree(s->train_items);
-    cudaFree(s->test_indptr); cudaFree(s->test_items); cudaFree(s->sums); cudaFree(s->dense);
+    cudaFree(s->test_indptr); cudaFree(s->test_items); cudaFree(s->sums); cudaFree(s->dense); cudaFree(s->glist);
     delete s;
     c->eval_scratch = nullptr;
 }

@@ -24,6 +24,8 @@ struct Ctx {
     int2 *clicks = nullptr;
     int *his = nullptr, *masks = nullptr;
     uint64_t n_samples = 0, max_his = 0;
+    unsigned long long *stage = nullptr;                  // uint64 staging of heat_set_dataset (+ 3 range flags)
+    size_t clicks_cap = 0, his_cap = 0, masks_cap = 0, stage_cap = 0;
     float *user_w = nullptr, *item_w = nullptr, *user_g = nullptr, *item_g = nullptr, *w0 = nullptr;
     float *h_user_w = nullptr, *h_item_w = nullptr, *h_w0 = nullptr;   // bound host buffers
     unsigned long long *chunk_counter = nullptr;
