@@ -15,10 +15,13 @@
 //   warp 0      TMA producer   A (users, hi+lo) once per block; B (items, hi+lo) ring of stages
 //   warp 1      MMA issuer     one elected thread, 3 x D/8 tcgen05.mma.kind::tf32 per item tile,
 //                              accumulators double/quad-buffered in TMEM; owns TMEM alloc/dealloc
-//   warps 2..5  epilogue       tcgen05.ld: thread = user row, NT consecutive item scores; a max-of-16
-//                              threshold vote per group, survivors appended to the row's candidate
-//                              buffer in shared memory; a full buffer is folded into the row's sorted
-//                              list by the whole warp (train-mask binary search + bitonic sort)
+//   warps 2..9  epilogue       two sets of four warps take alternate item tiles (two warps per scheduler
+//                              hide each other's latencies).  tcgen05.ld: thread = user row, NT
+//                              consecutive item scores; a max-of-16 threshold vote per group, survivors
+//                              appended to the (set, row) candidate buffer in shared memory; a full
+//                              buffer is folded into the (set, row) sorted list by the whole warp
+//                              (train-mask binary search, bitonic sort of the candidates, bitonic merge);
+//                              the sets exchange thresholds and set 0 merges the two lists at the end
 #include <algorithm>
 #include <cmath>
 #include <vector>
@@ -29,7 +32,7 @@ namespace heat {
 namespace {
 
 constexpr int EV_M = 128;          // users per CTA block = TMEM lanes
-constexpr int EV_THREADS = 192;    // 6 warps
+constexpr int EV_CAP = 32;         // candidate-buffer entries per (epilogue set, user row)
 constexpr int ACC_STAGES = 4;      // TMEM accumulator ring
 constexpr int MAX_B_STAGES = 4;
 
@@ -43,8 +46,8 @@ struct EvalParams {
     int *topk_ids;                 // [U, k]
     float *topk_scores;            // [U, k]
     float *dense_out;              // [U, I] when k == 0
-    unsigned long long *glist;     // [grid, 128, 32*sort_e - CAP] sorted lists of the user block in flight (L2-resident scratch)
-    int sort_e;                    // keys per lane in the compaction sort: 4, 8 or 16
+    unsigned long long *glist;     // [grid, 3, 128, 32*(sort_e-1)] sorted lists of the user block in flight (L2-resident scratch)
+    int sort_e;                    // keys per lane in the fold: 4, 8 or 16
 };
 
 // x -> hi = tf32(x) (round to nearest, low 13 mantissa bits zero), lo = tf32(x - hi)
@@ -69,8 +72,10 @@ struct EvalSmem {
     static constexpr int A_BYTES = 2 * KA * A_ATOM;         // hi + lo
     static constexpr int B_STAGE = 2 * KA * B_ATOM;         // hi + lo
     static constexpr int BAR_BYTES = 256;
-    static constexpr int CAP = NT >= 64 ? 64 : 32;          // candidate-buffer entries per user row
-    static size_t bytes(int stages, int k) { return 1024 + A_BYTES + (size_t)stages * B_STAGE + (k ? (size_t)CAP * EV_M * 8 : 0) + BAR_BYTES; }
+    static constexpr int NSETS = D >= 128 ? 1 : 2;          // epilogue warp sets (D = 128: shared memory holds one buffer set)
+    static constexpr int THREADS = 64 + NSETS * 128;
+    static constexpr int BUF_BYTES = NSETS * EV_CAP * EV_M * 8 + NSETS * EV_M * 8;   // candidate keys + shared thresholds
+    static size_t bytes(int stages, int k) { return 1024 + A_BYTES + (size_t)stages * B_STAGE + (k ? (size_t)BUF_BYTES : 0) + BAR_BYTES; }
 };
 
 // Top-k entries are 64-bit keys: order-preserving bits of the score in the high word, (0x7fffffff - item id) in the
@@ -88,132 +93,206 @@ __device__ __forceinline__ float topk_key_score(unsigned long long key)
     return __uint_as_float(u);
 }
 __device__ __forceinline__ int topk_key_id(unsigned long long key) { return 0x7fffffff - (int)(unsigned)key; }
+// the largest float below x (x finite or +inf; -inf stays -inf)
+__device__ __forceinline__ float float_below(float x)
+{
+    const unsigned u = __float_as_uint(x);
+    if (x > 0.f) return __uint_as_float(u - 1);
+    if (x == 0.f) return __uint_as_float(0x80000001u);
+    return x == -INFINITY ? x : __uint_as_float(u + 1);
+}
 
-// Bitonic sort, descending, of 32*E keys held E per lane in blocked order (element index = lane*E + i).
-template <int E>
-__device__ __forceinline__ void bitonic_sort_desc(unsigned long long (&key)[E], int lane)
+// Warp-wide sorting networks over keys held in STRIDED order: element index = i*32 + lane for register i.
+// Strides >= 32 are register-to-register, strides < 32 are shfl_xor exchanges.
+//
+// Ascending bitonic sort of registers [R0, R0+C) (32*C elements).
+template <int E, int R0, int C>
+__device__ __forceinline__ void bitonic_sort_asc(unsigned long long (&key)[E], int lane)
 {
 #pragma unroll
-    for (int size = 2; size <= 32 * E; size <<= 1) {
+    for (int size = 2; size <= 32 * C; size <<= 1) {
 #pragma unroll
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            if (stride >= E) {
-                const int lmask = stride / E;
-                const bool keep_max = (((lane * E) & size) == 0) == ((lane & lmask) == 0);
+            if (stride >= 32) {
+                const int rs = stride / 32;
 #pragma unroll
-                for (int i = 0; i < E; ++i) {
-                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[i], lmask);
-                    const bool take = keep_max ? (o > key[i]) : (o < key[i]);
-                    key[i] = take ? o : key[i];
+                for (int i = 0; i < C; ++i) {
+                    if ((i & rs) == 0) {
+                        const bool asc = ((i * 32) & size) == 0;
+                        const unsigned long long a = key[R0 + i], b = key[R0 + (i | rs)];
+                        const bool sw = asc ? (b < a) : (b > a);
+                        key[R0 + i] = sw ? b : a;
+                        key[R0 + (i | rs)] = sw ? a : b;
+                    }
                 }
             } else {
+                const bool lower = (lane & stride) == 0;
 #pragma unroll
-                for (int i = 0; i < E; ++i) {
-                    if ((i & stride) == 0) {
-                        const int j = i | stride;
-                        const bool desc = (((lane * E + i) & size) == 0);
-                        const unsigned long long a = key[i], b = key[j];
-                        const bool sw = desc ? (b > a) : (b < a);
-                        key[i] = sw ? b : a;
-                        key[j] = sw ? a : b;
-                    }
+                for (int i = 0; i < C; ++i) {
+                    const bool asc = (((i * 32) | lane) & size) == 0;
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[R0 + i], stride);
+                    const bool take = (asc == lower) ? (o < key[R0 + i]) : (o > key[R0 + i]);
+                    key[R0 + i] = take ? o : key[R0 + i];
                 }
             }
         }
     }
 }
+// Descending bitonic MERGE of all 32*E elements; the input must be bitonic (here: a descending list followed by
+// ascending candidates).
+template <int E>
+__device__ __forceinline__ void bitonic_merge_desc(unsigned long long (&key)[E], int lane)
+{
+#pragma unroll
+    for (int rs = E / 2; rs > 0; rs >>= 1) {
+#pragma unroll
+        for (int i = 0; i < E; ++i) {
+            if ((i & rs) == 0) {
+                const unsigned long long a = key[i], b = key[i | rs];
+                const bool sw = b > a;
+                key[i] = sw ? b : a;
+                key[i | rs] = sw ? a : b;
+            }
+        }
+    }
+#pragma unroll
+    for (int stride = 16; stride > 0; stride >>= 1) {
+        const bool lower = (lane & stride) == 0;
+#pragma unroll
+        for (int i = 0; i < E; ++i) {
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[i], stride);
+            const bool take = lower ? (o > key[i]) : (o < key[i]);
+            key[i] = take ? o : key[i];
+        }
+    }
+}
 
-// Per-lane (= per user row) state of the streaming top-k.  While the item tiles stream by, a lane only APPENDS the
-// scores that beat its row's threshold to the row's candidate buffer (one shared-memory store); the threshold is
-// the k-th best score as of the row's last compaction, so it lags -- that only admits a few extra candidates.
-struct RowState {
-    float thr;          // k-th best unmasked score at the last compaction (valid when full)
-    bool full;          // the row's list holds k unmasked items
-    bool has_list;      // the row's list in global scratch has been written for this user block
-    int cnt;            // candidates waiting in the buffer
-    long long tb, te;   // the user's train items [tb, te), sorted ascending (the -inf mask of metrics.py:21-24)
+// Per-lane (= per user row, per epilogue set) state of the streaming top-k lives in registers of the epilogue loop:
+//   thr   lower bound of the row's k-th best unmasked score (-inf until k items are known; +inf for padding rows)
+//   wptr  shared-memory address of the row's next free candidate slot (slot j of row r at buf + (j*128 + r)*8)
+//   cur   how many of the user's train items lie below the columns folded so far (forward-only cursor)
+// While the item tiles stream by, a lane only APPENDS the raw (score, column) pairs that beat its row's threshold
+// (two predicated shared-memory stores); the threshold is the k-th best score as of the row's last fold (or the
+// other set's), so it lags -- that only admits a few extra candidates.
+
+enum { FOLD_STREAM = 0, FOLD_LAST = 1, FOLD_OUTPUT = 2 };
+
+struct FoldArgs {
+    int E, k, lane, row0;                       // keys per lane in the fold, top-k size, lane, first row of the warp's quadrant
+    uint32_t buf_s;                             // shared-space address of the set's candidate buffers [EV_CAP][128] x 8 B
+    unsigned long long *glist;                  // the set's lists of the user block in flight [128][32*(E-1)]
+    const unsigned long long *other_list;       // FOLD_OUTPUT: the other set's finished lists (or null)
+    const int *train_items;
+    int u_base;                                 // first user of the block (FOLD_OUTPUT)
+    int *out_ids; float *out_scores;
+    unsigned long long *thr_pub;                // this set's published thresholds [128] (or null)
+    unsigned tag;                               // user block tag of the published thresholds
 };
 
-// Fold the candidate buffers of the rows in `rows` (bit r = row of lane r) into their sorted lists; the whole warp
-// works on one row at a time: the candidates that are train items of the user are dropped (binary search in the
-// user's sorted list -- deferred to here so that the streaming path never touches the CSR), list + candidates are
-// sorted as 32*E keys, the best LCAP = 32*E - CAP go back to the row's list (global scratch, L2-resident) and the
-// k-th one becomes the row's new threshold.  With `final` the first k entries are written out instead.
-template <int E, int CAP>
-__device__ __noinline__ void topk_compact(unsigned rows, RowState &st, int lane, int q, const unsigned long long *buf,
-                                          unsigned long long *glist, const int *__restrict__ train_items, int k, bool final,
-                                          int u_base, int *__restrict__ out_ids, float *__restrict__ out_scores)
+__device__ __forceinline__ unsigned long long lds64(uint32_t addr)
 {
-    constexpr int LCAP = 32 * E - CAP, LE = LCAP / 32, CE = CAP / 32;
-    const unsigned has = __ballot_sync(0xffffffffu, st.has_list);
+    unsigned long long v;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+
+// Fold the candidate buffers of the rows in `rows` (bit r = row of lane r) into their sorted lists; the whole warp
+// works on one row at a time.  Candidates that are train items of the user are dropped: candidates arrive in column
+// order and the user's list is sorted, so the warp reads the list 32 items at a time from the row's cursor (one
+// coalesced load) and every lane looks its column up by a 5-step shuffle binary search -- the streaming path never
+// touches the CSR.  The <= 32 survivors become keys, are sorted ascending and bitonic-merged with the row's
+// descending list of LCAP = 32*(E-1) keys (global scratch, L2-resident); the k-th key becomes the row's new
+// threshold.  FOLD_OUTPUT (end of the user block) also merges the other set's finished list, 32 keys at a time, and
+// writes the first k entries out instead of storing the list.
+// Returns the lane's new (threshold, cursor) pair; `cnt` of the folded rows is reset by the caller.
+template <int E>
+__device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, unsigned rows, float thr, int cnt, long long tb, int ntrain,
+                                                        int cur, unsigned has, int col_next, int mode)
+{
+    constexpr int LE = E - 1, LCAP = 32 * LE;
+    const int lane = A.lane, k = A.k;
+    const int *__restrict__ train_items = A.train_items;
     while (rows) {
         const int r = __ffs(rows) - 1;
         rows &= rows - 1;
-        const int row = q * 32 + r;
-        const int n = __shfl_sync(0xffffffffu, st.cnt, r);
-        const long long tb = __shfl_sync(0xffffffffu, st.tb, r), te = __shfl_sync(0xffffffffu, st.te, r);
+        const int row = A.row0 + r;
+        const int n = __shfl_sync(0xffffffffu, cnt, r);
+        const long long tbr = __shfl_sync(0xffffffffu, tb, r);
+        const int nr = __shfl_sync(0xffffffffu, ntrain, r);
+        int pos = __shfl_sync(0xffffffffu, cur, r);
         unsigned long long key[E];
-        unsigned long long *gl = glist + (size_t)row * LCAP;
+        unsigned long long *gl = A.glist + (size_t)row * LCAP;
 #pragma unroll
         for (int i = 0; i < LE; ++i) key[i] = ((has >> r) & 1u) ? __ldcg(gl + lane + 32 * i) : 0ull;
+        const unsigned long long raw = lane < n ? lds64(A.buf_s + (uint32_t)(lane * EV_M + row) * 8u) : 0ull;   // (column, score bits)
+        const int col = lane < n ? (int)(unsigned)raw : -1;
+        bool masked = false;
+        while (pos < nr) {
+            const int tv = pos + lane < nr ? __ldg(train_items + tbr + pos + lane) : 0x7fffffff;
+            int lo = 0;
 #pragma unroll
-        for (int i = 0; i < CE; ++i) {
-            const int j = lane + 32 * i;
-            unsigned long long c = j < n ? buf[j * EV_M + row] : 0ull;
-            if (c != 0ull && tb < te) {
-                const int col = 0x7fffffff - (int)(unsigned)c;
-                long long lo = tb, hi = te;
-                while (lo < hi) {
-                    const long long mid = (lo + hi) >> 1;
-                    if (__ldg(train_items + mid) < col) lo = mid + 1; else hi = mid;
-                }
-                if (lo < te && __ldg(train_items + lo) == col) c = 0ull;
+            for (int s = 16; s > 0; s >>= 1) {
+                const int tt = __shfl_sync(0xffffffffu, tv, lo + s - 1);
+                if (tt < col) lo += s;
             }
-            key[LE + i] = c;
+            masked |= __shfl_sync(0xffffffffu, tv, lo) == col;
+            const int adv = __popc(__ballot_sync(0xffffffffu, tv < col_next));
+            pos += adv;
+            if (adv < 32) break;
         }
-        bitonic_sort_desc<E>(key, lane);
-        // k-th best: element index k-1 = lane (k-1)/E, register (k-1)%E
+        key[LE] = (lane < n && !masked) ? topk_key(__uint_as_float((unsigned)(raw >> 32)), col) : 0ull;
+        bitonic_sort_asc<E, LE, 1>(key, lane);
+        bitonic_merge_desc<E>(key, lane);
+        if (mode == FOLD_OUTPUT && A.other_list) {
+            const unsigned long long *ol = A.other_list + (size_t)row * LCAP;
+            for (int c0 = 0; c0 < k; c0 += 32) {          // the other set's list is descending: read 32 keys reversed
+                key[LE] = __ldcg(ol + c0 + 31 - lane);
+                bitonic_merge_desc<E>(key, lane);
+            }
+        }
+        // k-th best: element index k-1 = register (k-1)/32, lane (k-1)%32
         unsigned long long kth = 0ull;
 #pragma unroll
-        for (int i = 0; i < E; ++i) kth = ((k - 1) % E == i) ? key[i] : kth;
-        kth = __shfl_sync(0xffffffffu, kth, (k - 1) / E);
-        if (final) {
-            const int u = u_base + row;
+        for (int i = 0; i < E; ++i) kth = ((k - 1) / 32 == i) ? key[i] : kth;
+        kth = __shfl_sync(0xffffffffu, kth, (k - 1) & 31);
+        if (mode == FOLD_OUTPUT) {
+            const int u = A.u_base + row;
 #pragma unroll
-            for (int i = 0; i < E; ++i) {
-                const int j = lane * E + i;
+            for (int i = 0; i < LE; ++i) {
+                const int j = i * 32 + lane;
                 if (j < k) {
-                    out_ids[(size_t)u * k + j] = key[i] ? topk_key_id(key[i]) : -1;
-                    if (out_scores) out_scores[(size_t)u * k + j] = key[i] ? topk_key_score(key[i]) : -INFINITY;
+                    A.out_ids[(size_t)u * k + j] = key[i] ? topk_key_id(key[i]) : -1;
+                    if (A.out_scores) A.out_scores[(size_t)u * k + j] = key[i] ? topk_key_score(key[i]) : -INFINITY;
                 }
             }
         } else {
 #pragma unroll
-            for (int i = 0; i < E; ++i) {
-                const int j = lane * E + i;
-                if (j < LCAP) __stcg(gl + j, key[i]);
-            }
+            for (int i = 0; i < LE; ++i) __stcg(gl + lane + 32 * i, key[i]);
         }
         if (lane == r) {
-            st.cnt = 0; st.has_list = true;
-            if (kth != 0ull) { st.thr = topk_key_score(kth); st.full = true; }
+            cur = pos;
+            if (kth != 0ull) {
+                thr = fmaxf(thr, topk_key_score(kth));
+                if (A.thr_pub) A.thr_pub[row] = ((unsigned long long)A.tag << 32) | __float_as_uint(thr);
+            }
         }
     }
     __syncwarp();
+    return ((unsigned long long)(unsigned)cur << 32) | __float_as_uint(thr);
 }
 
-template <int CAP>
-__device__ __forceinline__ void topk_compact_any(int E, unsigned rows, RowState &st, int lane, int q, const unsigned long long *buf,
-                                                 unsigned long long *glist, const int *train_items, int k, bool final, int u_base,
-                                                 int *out_ids, float *out_scores)
+// The ONE out-of-line copy of the fold (the streaming loop stays small enough for the instruction cache).
+__device__ __noinline__ unsigned long long topk_fold_dispatch(const FoldArgs &A, unsigned rows, float thr, int cnt, long long tb,
+                                                              int ntrain, int cur, unsigned has, int col_next, int mode)
 {
-    if (E == 4) topk_compact<4, CAP>(rows, st, lane, q, buf, glist, train_items, k, final, u_base, out_ids, out_scores);
-    else if (E == 8) topk_compact<8, CAP>(rows, st, lane, q, buf, glist, train_items, k, final, u_base, out_ids, out_scores);
-    else topk_compact<16, CAP>(rows, st, lane, q, buf, glist, train_items, k, final, u_base, out_ids, out_scores);
+    if (A.E == 4) return topk_fold<4>(A, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
+    if (A.E == 8) return topk_fold<8>(A, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
+    return topk_fold<16>(A, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
 }
 
 template <int D, int NT>
-__global__ void __launch_bounds__(EV_THREADS, 1)
+__global__ void __launch_bounds__((EvalSmem<D, NT>::THREADS), 1)
 eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
             const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo, const EvalParams P)
 {
@@ -226,8 +305,10 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t *sA = smem;                                       // [hi|lo][KA][128 x 128B]
     uint8_t *sB = sA + S::A_BYTES;                            // [stage][hi|lo][KA][NT x 128B]
-    unsigned long long *buf = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [CAP][128] candidate keys
-    uint64_t *bars = reinterpret_cast<uint64_t *>(buf + (P.k ? (size_t)S::CAP * EV_M : 0));
+    constexpr int NSETS = S::NSETS;
+    unsigned long long *buf = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [set][EV_CAP][128] candidate keys
+    unsigned long long *thr_sh = buf + (size_t)NSETS * EV_CAP * EV_M;                                          // [set][128] (user block tag, threshold)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(buf) + (P.k ? (size_t)S::BUF_BYTES : 0));
     uint64_t *full = bars, *empty = bars + MAX_B_STAGES;
     uint64_t *tfull = bars + 2 * MAX_B_STAGES, *tempty = tfull + ACC_STAGES;
     uint64_t *a_full = tempty + ACC_STAGES, *a_empty = a_full + 1;
@@ -244,6 +325,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+    if (P.k > 0 && threadIdx.x < NSETS * EV_M) thr_sh[threadIdx.x] = 0ull;      // tag 0 = no threshold published
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -309,70 +391,134 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
             }
         }
     } else {
-        // ================= epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =================
-        constexpr int CAP = S::CAP;
-        const int q = warp & 3;
+        // ================= epilogue: NSETS sets of four warps, TMEM lane quadrant = warp % 4 =================
+        const int set = (warp - 2) >> 2, q = warp & 3;
         const int row = q * 32 + lane;
-        const int k = P.k, E = P.sort_e;
-        unsigned long long *glist = P.glist + (size_t)blockIdx.x * EV_M * (32 * E - CAP);
-        unsigned long long *my = buf + row;
-        uint32_t it_acc = 0;
-        for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x) {
+        const int k = P.k;
+        const int lcap = 32 * (P.sort_e - 1);
+        // global scratch of this CTA: set 0's lists, then two generations of set 1's lists (set 0 reads generation g
+        // while set 1 may already be writing g+1; the accumulator ring keeps the sets within a few tiles of each other)
+        unsigned long long *gl_base = P.glist + (size_t)blockIdx.x * 3 * EV_M * lcap;
+        const uint32_t buf_s = ptx::smem_u32(buf) + (uint32_t)set * EV_CAP * EV_M * 8u;
+        const uint32_t my_s = buf_s + (uint32_t)row * 8u;                    // slot 0 of this lane's row; slots are 1 KiB apart
+        FoldArgs FA;
+        FA.E = P.sort_e; FA.k = k; FA.lane = lane; FA.row0 = q * 32; FA.buf_s = buf_s; FA.other_list = nullptr;
+        FA.train_items = P.train_items; FA.out_ids = P.topk_ids; FA.out_scores = P.topk_scores;
+        FA.thr_pub = (NSETS > 1 && k > 0) ? thr_sh + set * EV_M : nullptr;
+        unsigned rbi = 0;
+        for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++rbi) {
             const int u = rb * EV_M + row;
             const bool row_ok = u < P.U;
-            RowState st;
-            st.thr = row_ok ? -INFINITY : INFINITY; st.full = !row_ok; st.has_list = false; st.cnt = 0; st.tb = 0; st.te = 0;
-            if (row_ok && P.train_indptr) { st.tb = P.train_indptr[u]; st.te = P.train_indptr[u + 1]; }
-            for (int t = 0; t < P.n_item_tiles; ++t, ++it_acc) {
+            float thr = row_ok ? -INFINITY : INFINITY;
+            uint32_t wptr = my_s;
+            long long tb = 0;
+            int ntrain = 0, cur = 0;
+            unsigned has = 0;                                                 // rows of this warp whose list exists (uniform)
+            if (row_ok && k > 0 && P.train_indptr) { tb = P.train_indptr[u]; ntrain = (int)(P.train_indptr[u + 1] - tb); }
+            FA.glist = gl_base + (size_t)(set == 0 ? 0 : 1 + (rbi & 1)) * EV_M * lcap;
+            FA.u_base = rb * EV_M; FA.tag = rbi + 1;
+            const unsigned long long *thr_other = thr_sh + (set ^ 1) * EV_M + row;
+            float *dense_row = (k == 0 && row_ok) ? P.dense_out + (size_t)u * P.I : nullptr;
+            const uint32_t it0 = rbi * (uint32_t)P.n_item_tiles;
+
+            auto fold = [&](unsigned rows, int col_next, int mode) {
+                const unsigned long long ret = topk_fold_dispatch(FA, rows, thr, (int)((wptr - my_s) >> 10), tb, ntrain, cur, has, col_next, mode);
+                thr = __uint_as_float((unsigned)ret);
+                cur = (int)(unsigned)(ret >> 32);
+                if ((rows >> lane) & 1u) wptr = my_s;
+                has |= rows;
+            };
+            // One group of 16 consecutive scores of this lane's user.  Streaming path: ONE warp vote per group
+            // (max-of-16 against the row thresholds); only when some row of the warp has a survivor do the lanes look
+            // at their max-of-4 sub-groups and append the survivors; rows whose buffer may not take another group fold.
+            auto group = [&](uint32_t (&r)[16], int colg) {
+                float v[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+                if (k == 0) {
+                    if (dense_row) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (colg + i < P.I) dense_row[colg + i] = v[i];
+                    }
+                    return;
+                }
+                if (colg + 16 > P.I) {                              // ragged tail: the padding columns never qualify
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (colg + i >= P.I) v[i] = -INFINITY;
+                }
+                float m4[4];
+#pragma unroll
+                for (int h = 0; h < 4; ++h)
+                    m4[h] = fmaxf(fmaxf(v[4 * h], v[4 * h + 1]), fmaxf(v[4 * h + 2], v[4 * h + 3]));
+                const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+                if (!__any_sync(0xffffffffu, m > thr)) return;
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                    if (m4[h] > thr) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            if (v[4 * h + e] > thr) {
+                                sts32(wptr, (uint32_t)(colg + 4 * h + e));
+                                sts32(wptr + 4, __float_as_uint(v[4 * h + e]));
+                                wptr += EV_M * 8;
+                            }
+                        }
+                    }
+                }
+                const unsigned over = __ballot_sync(0xffffffffu, wptr > my_s + (EV_CAP - 16) * EV_M * 8);
+                if (over) fold(over, colg + 16, FOLD_STREAM);
+            };
+
+            for (int t = (int)((it0 + set) & (NSETS - 1)); t < P.n_item_tiles; t += NSETS) {
+                const uint32_t it_acc = it0 + t;
                 const int acc = it_acc % ACC_STAGES;
                 ptx::mbar_wait(&tfull[acc], (it_acc / ACC_STAGES) & 1);
                 ptx::tc_fence_after();
-                float v[NT];
-#pragma unroll
-                for (int c0 = 0; c0 < NT; c0 += 32)
-                    ptx::tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * NT + c0, *reinterpret_cast<float(*)[32]>(&v[c0]));
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&tempty[acc]);     // accumulator drained into registers
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * NT;
                 const int col0 = t * NT;
-                if (k == 0) {
-                    if (!row_ok) continue;
-                    float *out = P.dense_out + (size_t)u * P.I + col0;
-#pragma unroll
-                    for (int i = 0; i < NT; ++i)
-                        if (col0 + i < P.I) out[i] = v[i];
-                    continue;
+                if (NSETS > 1 && k > 0) {
+                    // adopt the other set's threshold for the same user block, one ulp lower: an equal score on this
+                    // side may carry the smaller item id and must still reach the final merge
+                    const unsigned long long o = *thr_other;
+                    if ((unsigned)(o >> 32) == rbi + 1) thr = fmaxf(thr, float_below(__uint_as_float((unsigned)o)));
                 }
-                if (col0 + NT > P.I) {                              // ragged last tile: the padding columns never qualify
-#pragma unroll
-                    for (int i = 0; i < NT; ++i)
-                        if (col0 + i >= P.I) v[i] = __int_as_float(0x7fc00000);
-                }
-                // Streaming path: ONE warp vote per 16 scores (max-of-16 against the row thresholds).  Only when some
-                // row of the warp has a survivor do the lanes test their 16 scores and append the survivors.
-#pragma unroll
-                for (int g = 0; g < NT; g += 16) {
-                    float m = v[g];
-#pragma unroll
-                    for (int e = 1; e < 16; ++e) m = fmaxf(m, v[g + e]);
-                    if (!__any_sync(0xffffffffu, !st.full || m > st.thr)) continue;
-#pragma unroll
-                    for (int e = 0; e < 16; ++e) {
-                        const float sc = v[g + e];
-                        const bool cand = st.full ? (sc > st.thr) : (sc == sc);
-                        if (cand) { my[st.cnt * EV_M] = topk_key(sc, col0 + g + e); ++st.cnt; }
-                    }
-                    const unsigned over = __ballot_sync(0xffffffffu, st.cnt > CAP - 16);
-                    if (over) {
+                // 16-column TMEM loads, software-pipelined: the next group is in flight while this one is filtered
+                uint32_t ra[16], rb16[16];
+                ptx::tmem_ld16_issue(taddr, ra);
+                ptx::tmem_ld_wait16(ra);
+#pragma unroll 1
+                for (int g = 0; g < NT; g += 32) {
+                    ptx::tmem_ld16_issue(taddr + g + 16, rb16);
+                    group(ra, col0 + g);
+                    ptx::tmem_ld_wait16(rb16);
+                    if (g + 32 < NT) {
+                        ptx::tmem_ld16_issue(taddr + g + 32, ra);
+                    } else {
+                        ptx::tc_fence_before();
                         __syncwarp();
-                        topk_compact_any<CAP>(E, over, st, lane, q, buf, glist, P.train_items, k, false, 0, nullptr, nullptr);
+                        if (lane == 0) ptx::mbar_arrive(&tempty[acc]);     // accumulator drained into registers
                     }
+                    group(rb16, col0 + g + 16);
+                    if (g + 32 < NT) ptx::tmem_ld_wait16(ra);
                 }
             }
             if (k > 0) {
                 const unsigned rows = __ballot_sync(0xffffffffu, row_ok);
                 __syncwarp();
-                topk_compact_any<CAP>(E, rows, st, lane, q, buf, glist, P.train_items, k, true, rb * EV_M, P.topk_ids, P.topk_scores);
+                if (NSETS == 1) {
+                    fold(rows, 0x7fffffff, FOLD_OUTPUT);
+                } else if (set == 1) {
+                    fold(rows, 0x7fffffff, FOLD_LAST);
+                    __threadfence_block();
+                    asm volatile("bar.arrive 1, 256;" ::: "memory");          // set 1's lists of this user block are complete
+                } else {
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    FA.other_list = gl_base + (size_t)(1 + (rbi & 1)) * EV_M * lcap;
+                    fold(rows, 0x7fffffff, FOLD_OUTPUT);
+                    FA.other_list = nullptr;
+                }
             }
         }
     }
@@ -525,17 +671,17 @@ int launch_eval(Ctx *c, EvalScratch *s, uint64_t u_begin, uint64_t u_count, Eval
     HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = std::min(P.n_row_blocks, c->num_sms);
     if (P.k > 0) {
-        // compaction sort width: 32*E keys >= k + CAP, E in {4, 8, 16}; the lists of the user blocks in flight
+        // fold width: 32*E keys = a sorted list of 32*(E-1) >= k keys + EV_CAP candidates, E in {4, 8, 16}
         int E = 4;
-        while (32 * E < P.k + S::CAP) E *= 2;
+        while (32 * (E - 1) < P.k) E *= 2;
         if (E > 16) return fail("evaluation kernel: top-k size too large");
         P.sort_e = E;
         size_t have = s->glist_elems;
-        if (int rc = ensure(&s->glist, &have, (size_t)grid * EV_M * (32 * E - S::CAP))) return rc;
+        if (int rc = ensure(&s->glist, &have, (size_t)grid * 3 * EV_M * 32 * (E - 1))) return rc;
         s->glist_elems = have;
         P.glist = s->glist;
     }
-    kern<<<grid, EV_THREADS, smem, c->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, P);
+    kern<<<grid, S::THREADS, smem, c->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, P);
     c->launches += 1;
     HEAT_CUDA(cudaGetLastError());
     return 0;
