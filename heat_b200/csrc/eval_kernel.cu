@@ -74,7 +74,7 @@ struct EvalSmem {
     static constexpr int BAR_BYTES = 256;
     static constexpr int NSETS = D >= 128 ? 1 : 2;          // epilogue warp sets (D = 128: shared memory holds one buffer set)
     static constexpr int THREADS = 64 + NSETS * 128;
-    static constexpr int BUF_BYTES = NSETS * EV_CAP * EV_M * 8 + NSETS * EV_M * 8;   // candidate keys + shared thresholds
+    static constexpr int BUF_BYTES = NSETS * EV_CAP * EV_M * 8 + 2 * NSETS * EV_M * 8;   // candidate pairs + published thresholds
     static size_t bytes(int stages, int k) { return 1024 + A_BYTES + (size_t)stages * B_STAGE + (k ? (size_t)BUF_BYTES : 0) + BAR_BYTES; }
 };
 
@@ -185,7 +185,8 @@ struct FoldArgs {
     const int *train_items;
     int u_base;                                 // first user of the block (FOLD_OUTPUT)
     int *out_ids; float *out_scores;
-    unsigned long long *thr_pub;                // this set's published thresholds [128] (or null)
+    unsigned long long *thr_pub;                // this set's published k-th scores [128] (or null)
+    unsigned long long *half_pub;               // this set's published ceil(k/2)-th scores [128]
     unsigned tag;                               // user block tag of the published thresholds
 };
 
@@ -256,6 +257,12 @@ __device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, unsig
 #pragma unroll
         for (int i = 0; i < E; ++i) kth = ((k - 1) / 32 == i) ? key[i] : kth;
         kth = __shfl_sync(0xffffffffu, kth, (k - 1) & 31);
+        // ceil(k/2)-th best: with the other set's ceil(k/2)-th it bounds the k-th best of the union (see the adoption)
+        const int ha = (k + 1) / 2 - 1;
+        unsigned long long hth = 0ull;
+#pragma unroll
+        for (int i = 0; i < E; ++i) hth = (ha / 32 == i) ? key[i] : hth;
+        hth = __shfl_sync(0xffffffffu, hth, ha & 31);
         if (mode == FOLD_OUTPUT) {
             const int u = A.u_base + row;
 #pragma unroll
@@ -272,9 +279,10 @@ __device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, unsig
         }
         if (lane == r) {
             cur = pos;
-            if (kth != 0ull) {
-                thr = fmaxf(thr, topk_key_score(kth));
-                if (A.thr_pub) A.thr_pub[row] = ((unsigned long long)A.tag << 32) | __float_as_uint(thr);
+            if (kth != 0ull) thr = fmaxf(thr, topk_key_score(kth));
+            if (A.thr_pub) {
+                if (kth != 0ull) A.thr_pub[row] = ((unsigned long long)A.tag << 32) | __float_as_uint(topk_key_score(kth));
+                if (hth != 0ull) A.half_pub[row] = ((unsigned long long)A.tag << 32) | __float_as_uint(topk_key_score(hth));
             }
         }
     }
@@ -307,7 +315,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
     uint8_t *sB = sA + S::A_BYTES;                            // [stage][hi|lo][KA][NT x 128B]
     constexpr int NSETS = S::NSETS;
     unsigned long long *buf = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [set][EV_CAP][128] candidate keys
-    unsigned long long *thr_sh = buf + (size_t)NSETS * EV_CAP * EV_M;                                          // [set][128] (user block tag, threshold)
+    unsigned long long *thr_sh = buf + (size_t)NSETS * EV_CAP * EV_M;                                          // [k-th | ceil(k/2)-th][set][128] (user block tag, score)
     uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(buf) + (P.k ? (size_t)S::BUF_BYTES : 0));
     uint64_t *full = bars, *empty = bars + MAX_B_STAGES;
     uint64_t *tfull = bars + 2 * MAX_B_STAGES, *tempty = tfull + ACC_STAGES;
@@ -325,7 +333,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
-    if (P.k > 0 && threadIdx.x < NSETS * EV_M) thr_sh[threadIdx.x] = 0ull;      // tag 0 = no threshold published
+    if (P.k > 0 && threadIdx.x < NSETS * EV_M) { thr_sh[threadIdx.x] = 0ull; thr_sh[NSETS * EV_M + threadIdx.x] = 0ull; }   // tag 0 = nothing published
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -405,6 +413,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         FA.E = P.sort_e; FA.k = k; FA.lane = lane; FA.row0 = q * 32; FA.buf_s = buf_s; FA.other_list = nullptr;
         FA.train_items = P.train_items; FA.out_ids = P.topk_ids; FA.out_scores = P.topk_scores;
         FA.thr_pub = (NSETS > 1 && k > 0) ? thr_sh + set * EV_M : nullptr;
+        FA.half_pub = thr_sh + (NSETS + set) * EV_M;
         unsigned rbi = 0;
         for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++rbi) {
             const int u = rb * EV_M + row;
@@ -430,7 +439,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
             };
             // One group of 16 consecutive scores of this lane's user.  Streaming path: ONE warp vote per group
             // (max-of-16 against the row thresholds); only when some row of the warp has a survivor do the lanes look
-            // at their max-of-4 sub-groups and append the survivors; rows whose buffer may not take another group fold.
+            // at their max-of-4 sub-groups and append the survivors.
             auto group = [&](uint32_t (&r)[16], int colg) {
                 float v[16];
 #pragma unroll
@@ -466,9 +475,10 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                             }
                         }
                     }
+                    // a row folds as soon as its buffer may not take four more candidates
+                    const unsigned over = __ballot_sync(0xffffffffu, wptr > my_s + (EV_CAP - 4) * EV_M * 8);
+                    if (over) fold(over, colg + 4 * h + 4, FOLD_STREAM);
                 }
-                const unsigned over = __ballot_sync(0xffffffffu, wptr > my_s + (EV_CAP - 16) * EV_M * 8);
-                if (over) fold(over, colg + 16, FOLD_STREAM);
             };
 
             for (int t = (int)((it0 + set) & (NSETS - 1)); t < P.n_item_tiles; t += NSETS) {
@@ -481,8 +491,13 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                 if (NSETS > 1 && k > 0) {
                     // adopt the other set's threshold for the same user block, one ulp lower: an equal score on this
                     // side may carry the smaller item id and must still reach the final merge
-                    const unsigned long long o = *thr_other;
+                    // Also: this set's ceil(k/2)-th best and the other set's are both exceeded-or-met by ceil(k/2) items of
+                    // disjoint column sets, so their minimum bounds the k-th best of the union -- for interleaved tiles
+                    // that is close to the exact threshold, which neither list alone knows.
+                    const unsigned long long o = *thr_other, oh = thr_other[NSETS * EV_M], mh = thr_sh[(NSETS + set) * EV_M + row];
                     if ((unsigned)(o >> 32) == rbi + 1) thr = fmaxf(thr, float_below(__uint_as_float((unsigned)o)));
+                    if ((unsigned)(oh >> 32) == rbi + 1 && (unsigned)(mh >> 32) == rbi + 1)
+                        thr = fmaxf(thr, float_below(fminf(__uint_as_float((unsigned)oh), __uint_as_float((unsigned)mh))));
                 }
                 // 16-column TMEM loads, software-pipelined: the next group is in flight while this one is filtered
                 uint32_t ra[16], rb16[16];
