@@ -103,16 +103,29 @@ __device__ __forceinline__ float float_below(float x)
 }
 
 // Warp-wide sorting networks over keys held in STRIDED order: element index = i*32 + lane for register i.
-// Strides >= 32 are register-to-register, strides < 32 are shfl_xor exchanges.
-//
+// Strides >= 32 are register-to-register, strides < 32 are shfl_xor exchanges.  All loops are counted so that they
+// unroll completely (the key array must stay in registers) and every compare-exchange is branch-free.
+template <int N> struct Log2 { static constexpr int v = 1 + Log2<N / 2>::v; };
+template <> struct Log2<1> { static constexpr int v = 0; };
+
+// keep the larger (want_max) or the smaller of (mine, other); equal keys are interchangeable
+__device__ __forceinline__ unsigned long long cx_pick(unsigned long long mine, unsigned long long other, bool want_max)
+{
+    const bool gt = other > mine;
+    return (gt == want_max) ? other : mine;
+}
+
 // Ascending bitonic sort of registers [R0, R0+C) (32*C elements).
 template <int E, int R0, int C>
 __device__ __forceinline__ void bitonic_sort_asc(unsigned long long (&key)[E], int lane)
 {
+    constexpr int LN = Log2<32 * C>::v;
 #pragma unroll
-    for (int size = 2; size <= 32 * C; size <<= 1) {
+    for (int ls = 1; ls <= LN; ++ls) {
+        const int size = 1 << ls;
 #pragma unroll
-        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int lt = ls - 1; lt >= 0; --lt) {
+            const int stride = 1 << lt;
             if (stride >= 32) {
                 const int rs = stride / 32;
 #pragma unroll
@@ -120,7 +133,7 @@ __device__ __forceinline__ void bitonic_sort_asc(unsigned long long (&key)[E], i
                     if ((i & rs) == 0) {
                         const bool asc = ((i * 32) & size) == 0;
                         const unsigned long long a = key[R0 + i], b = key[R0 + (i | rs)];
-                        const bool sw = asc ? (b < a) : (b > a);
+                        const bool sw = (b < a) == asc;
                         key[R0 + i] = sw ? b : a;
                         key[R0 + (i | rs)] = sw ? a : b;
                     }
@@ -131,8 +144,7 @@ __device__ __forceinline__ void bitonic_sort_asc(unsigned long long (&key)[E], i
                 for (int i = 0; i < C; ++i) {
                     const bool asc = (((i * 32) | lane) & size) == 0;
                     const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[R0 + i], stride);
-                    const bool take = (asc == lower) ? (o < key[R0 + i]) : (o > key[R0 + i]);
-                    key[R0 + i] = take ? o : key[R0 + i];
+                    key[R0 + i] = cx_pick(key[R0 + i], o, asc != lower);
                 }
             }
         }
@@ -143,8 +155,10 @@ __device__ __forceinline__ void bitonic_sort_asc(unsigned long long (&key)[E], i
 template <int E>
 __device__ __forceinline__ void bitonic_merge_desc(unsigned long long (&key)[E], int lane)
 {
+    constexpr int LE2 = Log2<E>::v;
 #pragma unroll
-    for (int rs = E / 2; rs > 0; rs >>= 1) {
+    for (int l = LE2 - 1; l >= 0; --l) {
+        const int rs = 1 << l;
 #pragma unroll
         for (int i = 0; i < E; ++i) {
             if ((i & rs) == 0) {
@@ -156,13 +170,13 @@ __device__ __forceinline__ void bitonic_merge_desc(unsigned long long (&key)[E],
         }
     }
 #pragma unroll
-    for (int stride = 16; stride > 0; stride >>= 1) {
+    for (int lt = 4; lt >= 0; --lt) {
+        const int stride = 1 << lt;
         const bool lower = (lane & stride) == 0;
 #pragma unroll
         for (int i = 0; i < E; ++i) {
             const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[i], stride);
-            const bool take = lower ? (o > key[i]) : (o < key[i]);
-            key[i] = take ? o : key[i];
+            key[i] = cx_pick(key[i], o, lower);
         }
     }
 }
