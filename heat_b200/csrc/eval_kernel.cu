@@ -32,7 +32,8 @@ namespace heat {
 namespace {
 
 constexpr int EV_M = 128;          // users per CTA block = TMEM lanes
-constexpr int EV_CAP = 32;         // candidate-buffer entries per (epilogue set, user row)
+constexpr int EV_CAP = 30;         // candidate-buffer entries per (epilogue set, user row): <= 32 (one key per lane in the fold);
+                                   // 30 leaves room for a third B stage at D = 64
 constexpr int ACC_STAGES = 4;      // TMEM accumulator ring
 constexpr int MAX_B_STAGES = 4;
 
@@ -191,16 +192,18 @@ __device__ __forceinline__ void bitonic_merge_desc(unsigned long long (&key)[E],
 
 enum { FOLD_STREAM = 0, FOLD_LAST = 1, FOLD_OUTPUT = 2 };
 
-struct FoldArgs {
-    int E, k, lane, row0;                       // keys per lane in the fold, top-k size, lane, first row of the warp's quadrant
-    uint32_t buf_s;                             // shared-space address of the set's candidate buffers [EV_CAP][128] x 8 B
-    unsigned long long *glist;                  // the set's lists of the user block in flight [128][32*(E-1)]
+struct FoldArgs {                               // the rarely read arguments (stack); the hot ones travel in registers
     const unsigned long long *other_list;       // FOLD_OUTPUT: the other set's finished lists (or null)
-    const int *train_items;
     int u_base;                                 // first user of the block (FOLD_OUTPUT)
     int *out_ids; float *out_scores;
-    unsigned long long *thr_pub;                // this set's published k-th scores [128] (or null)
     unsigned long long *half_pub;               // this set's published ceil(k/2)-th scores [128]
+};
+struct FoldHot {
+    int k, lane, row0;                          // top-k size, lane, first row of the warp's quadrant
+    uint32_t buf_s;                             // shared-space address of the set's candidate buffers [EV_CAP][128] x 8 B
+    unsigned long long *glist;                  // the set's lists of the user block in flight [128][32*(E-1)]
+    const int *train_items;
+    unsigned long long *thr_pub;                // this set's published k-th scores [128] (or null)
     unsigned tag;                               // user block tag of the published thresholds
 };
 
@@ -222,25 +225,25 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile(
 // writes the first k entries out instead of storing the list.
 // Returns the lane's new (threshold, cursor) pair; `cnt` of the folded rows is reset by the caller.
 template <int E>
-__device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, unsigned rows, float thr, int cnt, long long tb, int ntrain,
-                                                        int cur, unsigned has, int col_next, int mode)
+__device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, const FoldHot H, unsigned rows, float thr, int cnt,
+                                                        long long tb, int ntrain, int cur, unsigned has, int col_next, int mode)
 {
     constexpr int LE = E - 1, LCAP = 32 * LE;
-    const int lane = A.lane, k = A.k;
-    const int *__restrict__ train_items = A.train_items;
+    const int lane = H.lane, k = H.k;
+    const int *__restrict__ train_items = H.train_items;
     while (rows) {
         const int r = __ffs(rows) - 1;
         rows &= rows - 1;
-        const int row = A.row0 + r;
+        const int row = H.row0 + r;
         const int n = __shfl_sync(0xffffffffu, cnt, r);
         const long long tbr = __shfl_sync(0xffffffffu, tb, r);
         const int nr = __shfl_sync(0xffffffffu, ntrain, r);
         int pos = __shfl_sync(0xffffffffu, cur, r);
         unsigned long long key[E];
-        unsigned long long *gl = A.glist + (size_t)row * LCAP;
+        unsigned long long *gl = H.glist + (size_t)row * LCAP;
 #pragma unroll
         for (int i = 0; i < LE; ++i) key[i] = ((has >> r) & 1u) ? __ldcg(gl + lane + 32 * i) : 0ull;
-        const unsigned long long raw = lane < n ? lds64(A.buf_s + (uint32_t)(lane * EV_M + row) * 8u) : 0ull;   // (column, score bits)
+        const unsigned long long raw = lane < n ? lds64(H.buf_s + (uint32_t)(lane * EV_M + row) * 8u) : 0ull;   // (column, score bits)
         const int col = lane < n ? (int)(unsigned)raw : -1;
         bool masked = false;
         while (pos < nr) {
@@ -294,9 +297,9 @@ __device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, unsig
         if (lane == r) {
             cur = pos;
             if (kth != 0ull) thr = fmaxf(thr, topk_key_score(kth));
-            if (A.thr_pub) {
-                if (kth != 0ull) A.thr_pub[row] = ((unsigned long long)A.tag << 32) | __float_as_uint(topk_key_score(kth));
-                if (hth != 0ull) A.half_pub[row] = ((unsigned long long)A.tag << 32) | __float_as_uint(topk_key_score(hth));
+            if (H.thr_pub) {
+                if (kth != 0ull) H.thr_pub[row] = ((unsigned long long)H.tag << 32) | __float_as_uint(topk_key_score(kth));
+                if (hth != 0ull) A.half_pub[row] = ((unsigned long long)H.tag << 32) | __float_as_uint(topk_key_score(hth));
             }
         }
     }
@@ -305,12 +308,12 @@ __device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, unsig
 }
 
 // The ONE out-of-line copy of the fold (the streaming loop stays small enough for the instruction cache).
-__device__ __noinline__ unsigned long long topk_fold_dispatch(const FoldArgs &A, unsigned rows, float thr, int cnt, long long tb,
-                                                              int ntrain, int cur, unsigned has, int col_next, int mode)
+__device__ __noinline__ unsigned long long topk_fold_dispatch(const FoldArgs &A, const FoldHot H, int E, unsigned rows, float thr, int cnt,
+                                                              long long tb, int ntrain, int cur, unsigned has, int col_next, int mode)
 {
-    if (A.E == 4) return topk_fold<4>(A, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
-    if (A.E == 8) return topk_fold<8>(A, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
-    return topk_fold<16>(A, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
+    if (E == 4) return topk_fold<4>(A, H, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
+    if (E == 8) return topk_fold<8>(A, H, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
+    return topk_fold<16>(A, H, rows, thr, cnt, tb, ntrain, cur, has, col_next, mode);
 }
 
 template <int D, int NT>
@@ -424,10 +427,11 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         const uint32_t buf_s = ptx::smem_u32(buf) + (uint32_t)set * EV_CAP * EV_M * 8u;
         const uint32_t my_s = buf_s + (uint32_t)row * 8u;                    // slot 0 of this lane's row; slots are 1 KiB apart
         FoldArgs FA;
-        FA.E = P.sort_e; FA.k = k; FA.lane = lane; FA.row0 = q * 32; FA.buf_s = buf_s; FA.other_list = nullptr;
-        FA.train_items = P.train_items; FA.out_ids = P.topk_ids; FA.out_scores = P.topk_scores;
-        FA.thr_pub = (NSETS > 1 && k > 0) ? thr_sh + set * EV_M : nullptr;
+        FA.other_list = nullptr; FA.out_ids = P.topk_ids; FA.out_scores = P.topk_scores;
         FA.half_pub = thr_sh + (NSETS + set) * EV_M;
+        FoldHot FH;
+        FH.k = k; FH.lane = lane; FH.row0 = q * 32; FH.buf_s = buf_s; FH.train_items = P.train_items;
+        FH.thr_pub = (NSETS > 1 && k > 0) ? thr_sh + set * EV_M : nullptr;
         unsigned rbi = 0;
         for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++rbi) {
             const int u = rb * EV_M + row;
@@ -438,14 +442,14 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
             int ntrain = 0, cur = 0;
             unsigned has = 0;                                                 // rows of this warp whose list exists (uniform)
             if (row_ok && k > 0 && P.train_indptr) { tb = P.train_indptr[u]; ntrain = (int)(P.train_indptr[u + 1] - tb); }
-            FA.glist = gl_base + (size_t)(set == 0 ? 0 : 1 + (rbi & 1)) * EV_M * lcap;
-            FA.u_base = rb * EV_M; FA.tag = rbi + 1;
+            FH.glist = gl_base + (size_t)(set == 0 ? 0 : 1 + (rbi & 1)) * EV_M * lcap;
+            FA.u_base = rb * EV_M; FH.tag = rbi + 1;
             const unsigned long long *thr_other = thr_sh + (set ^ 1) * EV_M + row;
             float *dense_row = (k == 0 && row_ok) ? P.dense_out + (size_t)u * P.I : nullptr;
             const uint32_t it0 = rbi * (uint32_t)P.n_item_tiles;
 
             auto fold = [&](unsigned rows, int col_next, int mode) {
-                const unsigned long long ret = topk_fold_dispatch(FA, rows, thr, (int)((wptr - my_s) >> 10), tb, ntrain, cur, has, col_next, mode);
+                const unsigned long long ret = topk_fold_dispatch(FA, FH, P.sort_e, rows, thr, (int)((wptr - my_s) >> 10), tb, ntrain, cur, has, col_next, mode);
                 thr = __uint_as_float((unsigned)ret);
                 cur = (int)(unsigned)(ret >> 32);
                 if ((rows >> lane) & 1u) wptr = my_s;
