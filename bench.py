@@ -286,6 +286,29 @@ def run_gpu_arm(args, rank, world, local_rank):
     barrier()
     e2e_s = reduce_max(time.perf_counter() - t0)
     e2e_value = world * N * e2e_steps / e2e_s
+
+    # ---- evaluation leg ("eval ms" of BASELINE.json's metric): U.I^T on tcgen05 (3xTF32) fused with the masked top-50
+    #      and Recall/NDCG/HitRate, on the tables the epochs above trained; every rank evaluates its own user shard.
+    ev = None
+    if not args.no_eval:
+        ev_ms, ev_wall = [], []
+        res = None
+        for i in range(2 + 5):
+            flush_l2()
+            t0 = time.perf_counter()
+            res, _ = ctx.eval_metrics(d.train_indptr, d.train_items, d.test_indptr, d.test_items)
+            if i >= 2:
+                ev_wall.append((time.perf_counter() - t0) * 1e3); ev_ms.append(ctx.last_eval_ms())
+        ev_ms_max = reduce_max(float(np.mean(ev_ms)))
+        flops = 2.0 * d.num_users * d.num_items * D
+        tf32_peak = 1125.0                                   # TFLOP/s dense, nominal (half the bf16 rate; no measured TF32 peak on file)
+        ev = {"ms": ev_ms_max, "wall_ms_with_csr_upload": float(np.mean(ev_wall)), "users_per_gpu": int(d.num_users),
+              "items": int(d.num_items), "k": 50, "metrics": res,
+              "roofline": {"bound": "tensor", "achieved": 3 * flops / (ev_ms_max * 1e-3) / 1e12, "peak": tf32_peak, "unit": "TFLOP/s",
+                           "frac": 3 * flops / (ev_ms_max * 1e-3) / 1e12 / tf32_peak,
+                           "note": "executed TF32 flops (3 passes of 2*U*I*D: A_lo.B_hi + A_hi.B_lo + A_hi.B_hi); fp32-equivalent "
+                                   "work is a third of it; includes the TF32 split of both tables and the metrics kernel",
+                           "fp32_equivalent_tflops": flops / (ev_ms_max * 1e-3) / 1e12}}
     ctx.close()
 
     # ---- throughput mode, reported beside the headline: the warp-per-sample kernel on a full grid (thousands of
@@ -353,6 +376,8 @@ def run_gpu_arm(args, rank, world, local_rank):
             "update_mode": args.update_mode, "sync_interval": args.sync_interval if world > 1 else None,
             "engine": {0: "auto: CTA-per-sample kernel, parity-grade concurrency", 1: "warp-per-sample kernel, full grid",
                        2: "CTA-per-sample kernel"}[args.engine]}
+    if ev is not None:
+        line["eval"] = ev
     if thr is not None:
         thr["l2_frac"] = alg / (thr["kernel_ms"] * 1e-3) / 1e9 / l2_peak
         line["throughput_mode"] = thr
@@ -377,6 +402,7 @@ def main():
     ap.add_argument("--no-throughput-mode", action="store_true", help="skip the extra warp-per-sample full-grid measurement")
     ap.add_argument("--sync-interval", type=int, default=0, help="samples per GPU between item-delta all-reduces (0 = per epoch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-eval", action="store_true", help="skip the evaluation leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-step-seconds", type=float, default=4.0)
     ap.add_argument("--ncu-traffic", type=float, default=None, help="dram bytes per launch from profiles/ (ncu --set full)")

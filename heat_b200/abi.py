@@ -29,7 +29,7 @@ SYMBOLS = [
     "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
-    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free",
+    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state",
 ]
 
 
@@ -71,6 +71,8 @@ def lib():
         L.heat_train_range.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _f64p, _f32p]
         L.heat_zero_grad.argtypes = [C.c_void_p]
         L.heat_get_grads.argtypes = [C.c_void_p, _f32p, _f32p]
+        L.heat_save_state.argtypes = [C.c_void_p, C.c_char_p]
+        L.heat_load_state.argtypes = [C.c_void_p, C.c_char_p]
         L.heat_set_lr.argtypes = [C.c_void_p, C.c_float]
         L.heat_get_lr.argtypes = [C.c_void_p, _f32p]
         L.heat_get_epoch.argtypes = [C.c_void_p, _u64p]
@@ -210,6 +212,13 @@ class Context:
         gu = np.empty((self.U, self.D), np.float32); gi = np.empty((self.I, self.D), np.float32)
         _ck(lib().heat_get_grads(self._h, _ptr(gu, _f32p), _ptr(gi, _f32p)))
         return gu, gi
+
+    def save_state(self, path):
+        """Checkpoint {tables, grad rows, W0, epoch, LR} from the device to one file."""
+        _ck(lib().heat_save_state(self._h, os.fsencode(path)))
+
+    def load_state(self, path):
+        _ck(lib().heat_load_state(self._h, os.fsencode(path)))
 
     def set_lr(self, lr):
         _ck(lib().heat_set_lr(self._h, lr))

@@ -46,6 +46,10 @@ def main(argv=None):
     parser = argparse.ArgumentParser()
     parser.add_argument('--config', type=str, default='./benchmarks/AmazonBooks/MF_CCL/configs/config0.yaml')
     parser.add_argument('--dense-eval', action='store_true', help='evaluate0() + numpy metrics, like the reference')
+    parser.add_argument('--checkpoint', type=str, default=None, help='write {tables, grad rows, W0, epoch, LR} here after every '
+                        '--checkpoint-interval epochs (rank r writes PATH.rank<r> when WORLD_SIZE > 1)')
+    parser.add_argument('--checkpoint-interval', type=int, default=1)
+    parser.add_argument('--resume', type=str, default=None, help='continue from a --checkpoint file')
     args = parser.parse_args(argv)
     rank, size = int(os.environ.get('RANK', 0)), int(os.environ.get('WORLD_SIZE', 1))
 
@@ -90,7 +94,14 @@ def main(argv=None):
     eva_metrics = model_config.get('metrics') or ['Recall(k=20)']
     eval_interval = model_config['eval_interval']
     results = {}
-    for epoch in range(model_config['epochs']):
+    first_epoch = 0
+    suffix = f'.rank{rank}' if size > 1 else ''
+    if args.resume:
+        engine.load_checkpoint(args.resume + suffix)
+        first_epoch = int(engine.c_instance.epoch())
+        if rank == 0:
+            print(f'--- Resumed from {args.resume} at epoch {first_epoch} ---')
+    for epoch in range(first_epoch, model_config['epochs']):
         start_time = time.time()
         epoch_loss = engine.train_one_epoch()
         epoch_time = time.time() - start_time
@@ -98,6 +109,8 @@ def main(argv=None):
             n = train_data.click_dataset.shape[0]
             print(f'epoch: {epoch}; loss: {epoch_loss}; epoch_time: {epoch_time}; '
                   f'kernel_ms: {engine.c_instance.last_kernel_ms():.3f}; local samples/s: {n / max(epoch_time, 1e-9):.4g}')
+        if args.checkpoint and (epoch + 1) % max(args.checkpoint_interval, 1) == 0:
+            engine.save_checkpoint(args.checkpoint + suffix)
         if epoch > 0 and epoch % eval_interval == 0:
             if rank == 0:
                 print('--- Start evaluation ---')

@@ -1,4 +1,6 @@
 // heat_b200/csrc/heat_abi.cu -- the extern "C" surface of include/heat_b200.h.
+#include <algorithm>
+#include <cstdio>
 #include <cstring>
 #include <new>
 #include "heat_ctx.cuh"
@@ -294,6 +296,92 @@ int heat_get_grads(heat_ctx *ctx, float *user_g, float *item_g)
     if (item_g) HEAT_CUDA(cudaMemcpyAsync(item_g, c->item_g, c->cfg.num_items * D * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     HEAT_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
+}
+
+namespace {
+struct StateHeader {
+    char magic[8];
+    uint32_t version, emb_dim;
+    uint64_t num_users, num_items, epoch;
+    float l_r;
+    uint32_t pad[5];
+};
+static_assert(sizeof(StateHeader) == 64, "checkpoint header is 64 bytes");
+struct FileCloser { FILE *f; ~FileCloser() { if (f) fclose(f); } };
+}  // namespace
+
+int heat_save_state(heat_ctx *ctx, const char *path)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !path) return fail("heat_save_state: null argument");
+    if (!c->user_w) return fail("heat_save_state: no tables bound");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t D = c->cfg.emb_dim, U = c->cfg.num_users, I = c->cfg.num_items;
+    const std::string tmp = std::string(path) + ".tmp";
+    FileCloser fc{fopen(tmp.c_str(), "wb")};
+    if (!fc.f) return fail(std::string("heat_save_state: cannot open ") + tmp);
+    StateHeader h{};
+    memcpy(h.magic, "HEATB200", 8);
+    h.version = 1; h.emb_dim = (uint32_t)D; h.num_users = U; h.num_items = I; h.epoch = c->epoch; h.l_r = c->l_r;
+    if (fwrite(&h, sizeof(h), 1, fc.f) != 1) return fail("heat_save_state: write failed");
+    const struct { const float *p; size_t n; } parts[5] = {{c->user_w, U * D}, {c->item_w, I * D}, {c->w0, D * D}, {c->user_g, U * D}, {c->item_g, I * D}};
+    const size_t chunk = (size_t)16 << 20;                       // floats per staging copy (64 MiB, pinned)
+    float *stage = nullptr;
+    HEAT_CUDA(cudaMallocHost(&stage, chunk * sizeof(float)));
+    int rc = 0;
+    for (int i = 0; i < 5 && !rc; ++i)
+        for (size_t off = 0; off < parts[i].n && !rc; off += chunk) {
+            const size_t n = std::min(chunk, parts[i].n - off);
+            if (cudaMemcpyAsync(stage, parts[i].p + off, n * sizeof(float), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+                cudaStreamSynchronize(c->stream) != cudaSuccess)
+                rc = fail("heat_save_state: device read failed");
+            else if (fwrite(stage, sizeof(float), n, fc.f) != n)
+                rc = fail("heat_save_state: write failed");
+        }
+    cudaFreeHost(stage);
+    if (rc) return rc;
+    if (fclose(fc.f) != 0) { fc.f = nullptr; return fail("heat_save_state: close failed"); }
+    fc.f = nullptr;
+    if (rename(tmp.c_str(), path) != 0) return fail("heat_save_state: rename failed");   // a crash never leaves a torn file
+    return 0;
+}
+
+int heat_load_state(heat_ctx *ctx, const char *path)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !path) return fail("heat_load_state: null argument");
+    if (!c->user_w) return fail("heat_load_state: no tables bound");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    const size_t D = c->cfg.emb_dim, U = c->cfg.num_users, I = c->cfg.num_items;
+    FileCloser fc{fopen(path, "rb")};
+    if (!fc.f) return fail(std::string("heat_load_state: cannot open ") + path);
+    StateHeader h{};
+    if (fread(&h, sizeof(h), 1, fc.f) != 1 || memcmp(h.magic, "HEATB200", 8) != 0 || h.version != 1)
+        return fail("heat_load_state: not a heat_b200 checkpoint");
+    if (h.emb_dim != D || h.num_users != U || h.num_items != I)
+        return fail("heat_load_state: checkpoint shape differs from the context's config");
+    const struct { float *p; size_t n; } parts[5] = {{c->user_w, U * D}, {c->item_w, I * D}, {c->w0, D * D}, {c->user_g, U * D}, {c->item_g, I * D}};
+    const size_t chunk = (size_t)16 << 20;
+    float *stage = nullptr;
+    HEAT_CUDA(cudaMallocHost(&stage, chunk * sizeof(float)));
+    int rc = 0;
+    for (int i = 0; i < 5 && !rc; ++i)
+        for (size_t off = 0; off < parts[i].n && !rc; off += chunk) {
+            const size_t n = std::min(chunk, parts[i].n - off);
+            if (fread(stage, sizeof(float), n, fc.f) != n)
+                rc = fail("heat_load_state: file is truncated");
+            else if (cudaMemcpyAsync(parts[i].p + off, stage, n * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+                     cudaStreamSynchronize(c->stream) != cudaSuccess)
+                rc = fail("heat_load_state: device write failed");
+        }
+    cudaFreeHost(stage);
+    if (rc) return rc;
+    c->epoch = h.epoch; c->l_r = h.l_r;
+    if (c->item_base) {
+        HEAT_CUDA(cudaMemcpyAsync(c->item_base, c->item_w, I * D * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+        HEAT_CUDA(cudaMemcpyAsync(c->w0_base, c->w0, D * D * sizeof(float), cudaMemcpyDeviceToDevice, c->stream));
+    }
+    return heat_sync_to_host(ctx);
 }
 
 int heat_set_lr(heat_ctx *ctx, float l_r) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c) return fail("null context"); c->l_r = l_r; return 0; }

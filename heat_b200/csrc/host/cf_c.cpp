@@ -139,6 +139,9 @@ PYBIND11_MODULE(cf_c, cf_module)
             e.allreduce(out.mutable_data(), (int)out.size());
             return out;
         }, py::arg("values"))
+        .def("save_checkpoint", &Engine::save_checkpoint, py::arg("path"))
+        .def("load_checkpoint", &Engine::load_checkpoint, py::arg("path"))
+        .def("epoch", &Engine::epoch)
         .def("last_kernel_ms", &Engine::last_kernel_ms)
         .def("last_epoch_ms", &Engine::last_epoch_ms)
         .def("last_eval_ms", &Engine::last_eval_ms);

@@ -112,6 +112,14 @@ void Engine::evaluate_metrics(const int64_t *train_indptr, const int32_t *train_
 void Engine::comm_init(int rank, int world, const uint8_t uid[128]) { check(heat_comm_init(ctx_, rank, world, uid), "heat_comm_init"); }
 void Engine::set_sync_interval(uint64_t samples) { check(heat_set_sync_interval(ctx_, samples), "heat_set_sync_interval"); }
 void Engine::allreduce(double *vals, int n) { check(heat_comm_allreduce_f64(ctx_, vals, n), "heat_comm_allreduce_f64"); }
+void Engine::save_checkpoint(const std::string &path) { check(heat_save_state(ctx_, path.c_str()), "heat_save_state"); }
+void Engine::load_checkpoint(const std::string &path)
+{
+    check(heat_load_state(ctx_, path.c_str()), "heat_load_state");
+    uint64_t e = 0;
+    check(heat_get_epoch(ctx_, &e), "heat_get_epoch");
+    epoch_ = e;
+}
 float Engine::last_kernel_ms() { float v = 0; check(heat_last_kernel_ms(ctx_, &v), "heat_last_kernel_ms"); return v; }
 float Engine::last_epoch_ms() { float v = 0; check(heat_last_epoch_ms(ctx_, &v), "heat_last_epoch_ms"); return v; }
 float Engine::last_eval_ms() { float v = 0; check(heat_last_eval_ms(ctx_, &v), "heat_last_eval_ms"); return v; }

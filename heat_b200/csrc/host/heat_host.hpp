@@ -84,7 +84,10 @@ class Engine {
                           const int32_t *test_items, double out[6], double sums[7]);
     void comm_init(int rank, int world, const uint8_t uid[128]);
     void set_sync_interval(uint64_t samples);
+    void save_checkpoint(const std::string &path);   // {tables, grad rows, W0, epoch, LR} -> one file
+    void load_checkpoint(const std::string &path);   // restores the device state and the bound host tables
     void allreduce(double *vals, int n);
+    idx_t epoch() const { return epoch_; }       // epochs trained so far (restored by load_checkpoint)
     float last_kernel_ms();
     float last_epoch_ms();
     float last_eval_ms();

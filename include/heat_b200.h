@@ -119,6 +119,16 @@ int heat_last_epoch_ms(heat_ctx *ctx, float *ms);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 int heat_launch_count(heat_ctx *ctx, uint64_t *n);
 
+/* ---- checkpoint / resume (the reference has none: a killed job restarts) ----
+ * One binary file: a 64-byte header (magic "HEATB200", version, emb_dim, num_users, num_items,
+ * epoch, scheduled LR) followed by user_w, item_w, w0, user_g, item_g as raw fp32 in that order.
+ * heat_save_state reads the DEVICE state (no heat_sync_to_host needed); heat_load_state checks the
+ * shapes against the context's config, restores tables, grad rows, epoch and LR on the device
+ * and also refreshes the bound host buffers.  Training resumed from a file continues exactly
+ * as the uninterrupted run would (the Philox counter is a function of epoch and sample index). */
+int heat_save_state(heat_ctx *ctx, const char *path);
+int heat_load_state(heat_ctx *ctx, const char *path);
+
 /* ---- index contracts (bit-exact tests) --------------------------------------------- */
 /* Negative ids the device sampler draws for local samples [begin,end) of `epoch`:
  * out[(s-begin)*K + k].  replaces: UniformRandomNegativeSampler::ignore_pos_sampling

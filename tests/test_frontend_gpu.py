@@ -73,3 +73,23 @@ def test_in_place_numpy_contract_and_eval_paths_agree(tmp_path):
     ids, sc = eng.c_instance.evaluate_topk(50, *tr.csr())
     allm = metrics.metrics_from_topk(ids, *te.csr(num_users=cfg.num_users), ['MRR(k=50)', 'MAP(k=50)', 'Precision(k=10)'])
     assert all(np.isfinite(v) for v in allm.values())
+
+
+def test_cli_checkpoint_resume_and_full_metric_list(tmp_path, capsys):
+    """--checkpoint / --resume and the YAML `metrics` list beyond Recall/NDCG/HitRate
+    (row 4: Precision, F1, MRR, MAP, NormalizedRecall from the fused top-k lists)."""
+    from heat_b200.cf import main as cf_main
+    d, cfg = write_case(tmp_path, epochs=3, max_blocks=8, warps_per_block=4)
+    ck = str(tmp_path / "run.ckpt")
+    cf_main.main(["--config", cfg, "--checkpoint", ck])
+    capsys.readouterr()
+    import yaml as _y
+    c = _y.safe_load(open(cfg))
+    c["model_config"]["epochs"] = 5
+    c["model_config"]["metrics"] = ['Recall(k=20)', 'Precision(k=10)', 'F1(k=20)', 'MRR(k=50)', 'MAP(k=50)', 'NormalizedRecall(k=20)']
+    open(cfg, "w").write(_y.safe_dump(c))
+    res = cf_main.main(["--config", cfg, "--resume", ck])
+    out = capsys.readouterr().out
+    assert "Resumed from" in out and "at epoch 3" in out and "epoch: 3; loss:" in out and "epoch: 0; loss:" not in out
+    assert set(res) == set(c["model_config"]["metrics"])
+    assert res['Recall(k=20)'] > 0.05 and all(np.isfinite(v) for v in res.values())

@@ -214,3 +214,60 @@ def test_full_size_amazon_shape_properties():
     ctx.sync_to_host()
     assert all(np.isfinite(x).all() for x in t)
     assert ms < 2000.0     # the north-star's < 2 s epoch
+
+
+def test_checkpoint_resume_continues_bit_identically(tmp_path):
+    """{tables, grad rows, W0, epoch, LR} saved from the device mid-run; a NEW context that
+    loads the file continues exactly as the uninterrupted run (deterministic mode: one block, file order)."""
+    g = load_golden(TRAIN_CASES[0])
+    N = g["clicks"].shape[0]
+
+    def run(split):
+        uw, iw, w0 = fresh_tables(g)
+        ctx = make_ctx(g, deterministic=True, milestones=(1,))
+        ctx.bind_tables(uw, iw, w0)
+        ctx.train_epoch()                       # epoch 0, LR 1e-2
+        ctx.train_range(0, N // 2)              # half of epoch 1: grad rows are non-zero here
+        if split:
+            path = str(tmp_path / "state.ckpt")
+            ctx.save_state(path)
+            ctx.close()
+            uw, iw, w0 = (np.zeros_like(a) for a in (uw, iw, w0))
+            ctx = make_ctx(g, deterministic=True, milestones=(1,))
+            ctx.bind_tables(uw, iw, w0)
+            ctx.load_state(path)
+            assert ctx.get_epoch() == 1 and np.abs(uw).max() > 0       # bound host tables refreshed by the load
+        ctx.train_range(N // 2, N)
+        loss = ctx.train_epoch()                # epoch 1 again from the counter's point of view: LR schedule applies
+        ctx.sync_to_host()
+        gu, gi = ctx.grads()
+        out = (uw.copy(), iw.copy(), w0.copy(), gu, gi, loss, ctx.get_lr(), ctx.get_epoch())
+        ctx.close()
+        return out
+
+    a, b = run(False), run(True)
+    for x, y in zip(a[:5], b[:5]):
+        assert np.array_equal(x, y)
+    assert a[5:] == b[5:]
+
+
+def test_checkpoint_rejects_wrong_shape_and_garbage(tmp_path):
+    g = load_golden(TRAIN_CASES[0])
+    uw, iw, w0 = fresh_tables(g)
+    ctx = make_ctx(g)
+    ctx.bind_tables(uw, iw, w0)
+    path = str(tmp_path / "s.ckpt")
+    ctx.save_state(path)
+    U, D = uw.shape
+    other = abi.Context(D, int(g["K"]), U + 1, iw.shape[0])
+    other.bind_tables(np.zeros((U + 1, D), np.float32), iw.copy(), w0.copy())
+    with pytest.raises(abi.HeatError, match="shape differs"):
+        other.load_state(path)
+    bad = tmp_path / "bad.ckpt"
+    bad.write_bytes(b"not a checkpoint" * 8)
+    with pytest.raises(abi.HeatError, match="not a heat_b200 checkpoint"):
+        ctx.load_state(str(bad))
+    with open(path, "r+b") as f:
+        f.truncate(64 + 100)
+    with pytest.raises(abi.HeatError, match="truncated"):
+        ctx.load_state(path)
