@@ -29,7 +29,7 @@ SYMBOLS = [
     "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
-    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state",
+    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close",
 ]
 
 
@@ -71,6 +71,9 @@ def lib():
         L.heat_train_range.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _f64p, _f32p]
         L.heat_zero_grad.argtypes = [C.c_void_p]
         L.heat_get_grads.argtypes = [C.c_void_p, _f32p, _f32p]
+        L.heat_clickfile_open.argtypes = [C.c_char_p, C.c_char, C.POINTER(C.c_void_p), _u64p, _u64p]
+        L.heat_clickfile_read.argtypes = [C.c_void_p, _i64p, _i64p, _i64p]
+        L.heat_clickfile_close.argtypes = [C.c_void_p]
         L.heat_save_state.argtypes = [C.c_void_p, C.c_char_p]
         L.heat_load_state.argtypes = [C.c_void_p, C.c_char_p]
         L.heat_set_lr.argtypes = [C.c_void_p, C.c_float]
@@ -134,6 +137,20 @@ def probe_l2_bandwidth(device=0, nbytes=74 << 20, iters=200):
     g = C.c_double()
     _ck(lib().heat_probe_l2_bandwidth(device, nbytes, iters, C.byref(g)))
     return g.value
+
+
+def parse_clickfile(path, separator=" "):
+    """LightGCN-format file -> (row_users int64 [R], row_indptr int64 [R+1], items int64 [nnz]) in file order,
+    parsed natively with one thread per core (heat_clickfile_*; host code, needs no GPU)."""
+    h, rows, nnz = C.c_void_p(), C.c_uint64(), C.c_uint64()
+    sep = separator.encode()[:1] or b" "
+    _ck(lib().heat_clickfile_open(os.fsencode(path), sep, C.byref(h), C.byref(rows), C.byref(nnz)))
+    try:
+        users = np.empty(rows.value, np.int64); indptr = np.empty(rows.value + 1, np.int64); items = np.empty(nnz.value, np.int64)
+        _ck(lib().heat_clickfile_read(h, _ptr(users, _i64p), _ptr(indptr, _i64p), _ptr(items, _i64p)))
+    finally:
+        lib().heat_clickfile_close(h)
+    return users, indptr, items
 
 
 def philox_draw(seed, epoch, sample, k, num_items):

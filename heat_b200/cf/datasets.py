@@ -7,9 +7,11 @@ File format (datasets.py:31-40): one line per user, `user item item ...`.  Array
 one; mask = min(len, max_his).  The reference samples with an unseeded `random`; here the RNG is
 seeded from the config (`seed`, default 2022) so runs are reproducible.
 
-Differences from the reference, both deliberate: parsing is vectorised into a CSR (indptr, items)
-instead of python lists of pairs, and a rank takes its user range by slicing (`SubClickDataset`)
-without rank 0 pickling shards to the others (main.py:55-69).
+Differences from the reference, both deliberate: the file is parsed natively (`cf_c.modules.datasets.parse_clicks`
+-> heat_clickfile_*, one thread per core) into a CSR (indptr, items) instead of python lists of pairs built line
+by line, the CSR-by-user and history arrays are built with vectorised numpy (python only samples the users that
+have more than max_his items), and a rank takes its user range by slicing (`SubClickDataset`) without rank 0
+pickling shards to the others (main.py:55-69).
 """
 import random
 
@@ -29,23 +31,42 @@ class Dataset(CPPBase):
 
 
 def _history(indptr, items, max_his, seed):
+    """datasets.py:47-61.  Users below max_his items (the bulk) are filled by one gather; only the users with
+    >= max_his items go through python's `random.sample`, in user order (the seeded stream is unchanged)."""
     rnd = random.Random(seed)
     num_users = indptr.size - 1
-    his = np.zeros((num_users, max_his), dtype=np.uint64)
-    masks = np.zeros((num_users, 1), dtype=np.uint64)
-    for u in range(num_users):
-        row = items[indptr[u]:indptr[u + 1]]
-        n = row.size
-        if n >= max_his:
-            his[u] = rnd.sample(row.tolist(), max_his)
-            masks[u, 0] = max_his
-        elif n > 0:
-            his[u, :n] = row
-            his[u, n:] = row[-1]
-            masks[u, 0] = n
-        else:
-            print(f"Warning {u} has 0 items !!! ")
+    n = np.diff(indptr).astype(np.int64)
+    masks = np.minimum(n, max_his).astype(np.uint64).reshape(-1, 1)
+    if items.size:
+        j = np.minimum(np.arange(max_his, dtype=np.int64)[None, :], np.maximum(n, 1)[:, None] - 1)
+        his = items[np.minimum(indptr[:-1, None] + j, items.size - 1)].astype(np.uint64)
+        his[n == 0] = 0
+    else:
+        his = np.zeros((num_users, max_his), dtype=np.uint64)
+    for u in np.nonzero(n >= max_his)[0]:
+        his[u] = rnd.sample(items[indptr[u]:indptr[u + 1]].tolist(), max_his)
+    for u in np.nonzero(n == 0)[0][:20]:
+        print(f"Warning {u} has 0 items !!! ")
     return his, masks
+
+
+def parse_python(file_path, separator=' '):
+    """The reference's line-by-line reader (datasets.py:31-40), kept as the checker of the native one."""
+    users, rows = [], []
+    with open(file_path, mode='r') as f:
+        for line in f:
+            line = line.strip()
+            if not line:
+                continue
+            if separator != ' ':
+                line = line.replace(separator, ' ')
+            vals = np.array(line.split(), dtype=np.int64)
+            users.append(int(vals[0]))
+            rows.append(vals[1:])
+    counts = np.array([r.size for r in rows], dtype=np.int64)
+    indptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    items = np.concatenate(rows).astype(np.int64) if rows else np.zeros(0, np.int64)
+    return np.asarray(users, dtype=np.int64), indptr, items
 
 
 class ClickDataset(Dataset):
@@ -55,40 +76,27 @@ class ClickDataset(Dataset):
         self.file_path = file_path
         self.max_his = config.max_his
         self.rank = 0
-        users, rows = [], []
-        with open(file_path, mode='r') as f:
-            for line in f:
-                line = line.strip()
-                if not line:
-                    continue
-                if separator != ' ':
-                    line = line.replace(separator, ' ')
-                vals = np.array(line.split(), dtype=np.int64)
-                users.append(int(vals[0]))
-                rows.append(vals[1:])
-        users = np.asarray(users, dtype=np.int64)
+        users, file_indptr, file_items = cf_c.modules.datasets.parse_clicks(file_path, separator)
         self.num_users = int(users.size)
         if self.num_users and (users.min() != 0 or users.max() != self.num_users - 1 or np.unique(users).size != self.num_users):
             print('Warning user_id is not continuous! ')
         # rows are stored at their user id, samples stay in FILE order (engine.cpp:330-331 walks them that way)
-        self._file_users = users
-        counts = np.array([r.size for r in rows], dtype=np.int64)
-        self._file_indptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
-        self._file_items = np.concatenate(rows).astype(np.int64) if rows else np.zeros(0, np.int64)
+        self._file_users, self._file_indptr, self._file_items = users, file_indptr, file_items
         self.num_items = int(np.unique(self._file_items).size)
         self._finish(config, is_train='train' in file_path)
 
     def _finish(self, config, is_train):
         n_rows = max(self.num_users, int(self._file_users.max()) + 1 if self._file_users.size else 0)
-        indptr = np.zeros(n_rows + 1, np.int64)
-        indptr[self._file_users + 1] = np.diff(self._file_indptr)
-        self.indptr = np.cumsum(indptr)
-        items = np.empty(self._file_items.size, np.int32)
-        for j, u in enumerate(self._file_users):          # CSR by user id (identity when the file is sorted)
-            items[self.indptr[u]:self.indptr[u + 1]] = self._file_items[self._file_indptr[j]:self._file_indptr[j + 1]]
-        self.items = items
+        per_user = np.bincount(self._file_users, weights=np.diff(self._file_indptr), minlength=n_rows).astype(np.int64)
+        self.indptr = np.concatenate([[0], np.cumsum(per_user)]).astype(np.int64)
+        # CSR by user id: a stable sort of the file's (user, item) pairs by user (identity when the file is sorted)
+        pair_user = np.repeat(self._file_users, np.diff(self._file_indptr))
+        if self._file_users.size and np.all(self._file_users[1:] > self._file_users[:-1]):
+            self.items = self._file_items.astype(np.int32)
+        else:
+            self.items = self._file_items[np.argsort(pair_user, kind="stable")].astype(np.int32)
         self.click_dataset = np.empty((self._file_items.size, 2), dtype=np.uint64)
-        self.click_dataset[:, 0] = np.repeat(self._file_users, np.diff(self._file_indptr)).astype(np.uint64)
+        self.click_dataset[:, 0] = pair_user.astype(np.uint64)
         self.click_dataset[:, 1] = self._file_items.astype(np.uint64)
         self.his_items, self.masks = _history(self.indptr, self.items, self.max_his, getattr(config, "seed", 2022))
         self.gen_dataset_info()

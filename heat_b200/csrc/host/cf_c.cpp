@@ -66,6 +66,19 @@ PYBIND11_MODULE(cf_c, cf_module)
         .def_readwrite("data_rows", &ClickDataset::data_rows)
         .def_readwrite("max_his", &ClickDataset::max_his);
 
+    // additive: native LightGCN-format reader (heat_clickfile_*, include/heat_b200.h) behind datasets.ClickDataset
+    datasets.def("parse_clicks", [](const std::string &path, const std::string &separator) {
+        heat_clickfile *f = nullptr;
+        uint64_t rows = 0, nnz = 0;
+        if (heat_clickfile_open(path.c_str(), separator.empty() ? ' ' : separator[0], &f, &rows, &nnz) != 0)
+            throw std::runtime_error(heat_last_error());
+        py::array_t<int64_t> users((py::ssize_t)rows), indptr((py::ssize_t)rows + 1), items((py::ssize_t)nnz);
+        const int rc = heat_clickfile_read(f, users.mutable_data(), indptr.mutable_data(), items.mutable_data());
+        heat_clickfile_close(f);
+        if (rc != 0) throw std::runtime_error(heat_last_error());
+        return py::make_tuple(users, indptr, items);
+    }, py::arg("path"), py::arg("separator") = " ");
+
     py::module_ models = m.def_submodule("models", "models");
     py::class_<Model, std::shared_ptr<Model>>(models, "Model");
     py::class_<MatrixFactorization, Model, std::shared_ptr<MatrixFactorization>>(models, "MatrixFactorization")

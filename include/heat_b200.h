@@ -119,6 +119,17 @@ int heat_last_epoch_ms(heat_ctx *ctx, float *ms);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 int heat_launch_count(heat_ctx *ctx, uint64_t *n);
 
+/* ---- dataset ingest (host code) ----------------------------------
+ * replaces: the per-line Python parser of cf_cpu/cf/datasets.py:31-40.  LightGCN format, one line per
+ * user: `user item item ...` (fields separated by `separator` and/or blanks, empty lines skipped).
+ * heat_clickfile_open parses the whole file with one thread per core and reports the row and
+ * interaction counts; heat_clickfile_read fills caller arrays in FILE order: row_users [num_rows],
+ * row_indptr [num_rows+1], items [nnz]; heat_clickfile_close frees the handle. */
+typedef struct heat_clickfile heat_clickfile;
+int heat_clickfile_open(const char *path, char separator, heat_clickfile **out, uint64_t *num_rows, uint64_t *nnz);
+int heat_clickfile_read(heat_clickfile *f, int64_t *row_users, int64_t *row_indptr, int64_t *items);
+int heat_clickfile_close(heat_clickfile *f);
+
 /* ---- checkpoint / resume (the reference has none: a killed job restarts) ----
  * One binary file: a 64-byte header (magic "HEATB200", version, emb_dim, num_users, num_items,
  * epoch, scheduled LR) followed by user_w, item_w, w0, user_g, item_g as raw fp32 in that order.

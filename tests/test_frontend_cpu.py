@@ -96,3 +96,55 @@ def test_all_nine_host_metrics_match_the_reference_module():
         ref = rm.evaluate_metrics(a, b, sim.copy(), names)
     for n in names:
         assert abs(mine[n] - ref[n]) < 1e-9, (n, mine[n], ref[n])
+
+
+def test_native_click_parser_matches_the_reference_line_reader(tmp_path):
+    """heat_clickfile_* (C ABI, one thread per core) against the reference's per-line python
+    reader (datasets.py:31-40) -- blank lines, tabs / CRLF, a custom separator, unsorted users, a user without
+    items, a file large enough to be cut into per-thread chunks, and the error path."""
+    from heat_b200 import abi
+    from heat_b200.cf import datasets
+    rng = np.random.default_rng(5)
+    small = tmp_path / "small.txt"
+    small.write_text("3 10 11 12\n\n0 5\n2\n1 7 8\t9 \r\n")
+    for got in (abi.parse_clickfile(str(small)), datasets.cf_c.modules.datasets.parse_clicks(str(small), " ")):
+        want = datasets.parse_python(str(small))
+        for g, w in zip(got, want):
+            assert np.array_equal(g, w)
+    assert abi.parse_clickfile(str(small))[0].tolist() == [3, 0, 2, 1]
+    comma = tmp_path / "comma.txt"
+    comma.write_text("0,4,5\n1,6\n")
+    u, ip, it = abi.parse_clickfile(str(comma), ",")
+    assert u.tolist() == [0, 1] and ip.tolist() == [0, 2, 3] and it.tolist() == [4, 5, 6]
+    big = tmp_path / "big.txt"
+    with open(big, "w") as f:
+        for user in range(60000):
+            f.write(" ".join([str(user)] + [str(int(x)) for x in rng.integers(0, 10**6, int(rng.integers(1, 40)))]) + "\n")
+    assert big.stat().st_size > (1 << 20)
+    for g, w in zip(abi.parse_clickfile(str(big)), datasets.parse_python(str(big))):
+        assert np.array_equal(g, w)
+    bad = tmp_path / "bad.txt"
+    bad.write_text("0 1 2\n1 x 3\n")
+    with pytest.raises(abi.HeatError, match=r"bad.txt:2: unexpected character 'x'"):
+        abi.parse_clickfile(str(bad))
+    with pytest.raises(abi.HeatError, match="cannot open"):
+        abi.parse_clickfile(str(tmp_path / "missing.txt"))
+
+
+def test_history_arrays_follow_the_reference_rule():
+    """datasets.py:47-61: >= max_his items -> a sample of max_his of them (no repeats, all from the user's list);
+    fewer -> all items in order padded with the last; mask = min(len, max_his)."""
+    from heat_b200.cf import datasets
+    rng = np.random.default_rng(1)
+    n = np.array([0, 1, 5, 8, 9, 30], dtype=np.int64)
+    indptr = np.concatenate([[0], np.cumsum(n)])
+    items = rng.permutation(1000)[:indptr[-1]].astype(np.int32)
+    his, masks = datasets._history(indptr, items, 8, seed=3)
+    assert masks[:, 0].tolist() == [0, 1, 5, 8, 8, 8]
+    assert his[1].tolist() == [items[0]] * 8
+    assert his[2].tolist() == items[1:6].tolist() + [items[5]] * 3
+    for u in (3, 4, 5):
+        row = items[indptr[u]:indptr[u + 1]]
+        assert len(set(his[u].tolist())) == 8 and set(his[u].tolist()) <= set(row.tolist())
+    again, _ = datasets._history(indptr, items, 8, seed=3)
+    assert np.array_equal(his, again)
