@@ -29,7 +29,7 @@ SYMBOLS = [
     "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
-    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close",
+    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw",
 ]
 
 
@@ -44,6 +44,7 @@ class HeatConfig(C.Structure):
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
         ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
         ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("engine", C.c_uint32), ("max_blocks", C.c_uint32),
+        ("tile_sampler", C.c_uint32),
     ]
 
 
@@ -88,6 +89,8 @@ def lib():
         L.heat_history_indices.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _u64p, _u64p]
         L.heat_philox_draw.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64]
         L.heat_philox_draw.restype = C.c_uint64
+        L.heat_tile_draw.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64]
+        L.heat_tile_draw.restype = C.c_uint64
         L.heat_eval_dense.argtypes = [C.c_void_p, _f32p]
         L.heat_eval_topk.argtypes = [C.c_void_p, C.c_uint32, _i64p, _i32p, _i32p, _f32p]
         L.heat_eval_metrics.argtypes = [C.c_void_p, _i64p, _i32p, _i64p, _i32p, _f64p, _f64p]
@@ -153,6 +156,11 @@ def parse_clickfile(path, separator=" "):
     return users, indptr, items
 
 
+def tile_draw(seed, epoch, sample, k, num_items, tile_size, refresh_interval):
+    """Host twin of the device sampler with the hot-tile mapping (tile_size 0 = uniform)."""
+    return int(lib().heat_tile_draw(seed, epoch, sample, k, num_items, tile_size, refresh_interval))
+
+
 def philox_draw(seed, epoch, sample, k, num_items):
     return int(lib().heat_philox_draw(seed, epoch, sample, k, num_items))
 
@@ -163,7 +171,7 @@ class Context:
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
                  warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, history_mode=0, engine=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
-                 device=0):
+                 tile_sampler=0, device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
                          train_size=0, neg_sampler=neg_sampler, tile_size=tile_size,
@@ -172,7 +180,7 @@ class Context:
                          sample_offset=sample_offset, chunk=chunk, deterministic=int(bool(deterministic)),
                          w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
                          max_blocks=max_blocks, update_mode=update_mode,
-                         sync_average=sync_average, history_mode=history_mode, engine=engine)
+                         sync_average=sync_average, history_mode=history_mode, engine=engine, tile_sampler=tile_sampler)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0

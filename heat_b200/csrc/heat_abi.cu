@@ -69,6 +69,7 @@ TrainParams index_params(Ctx *c, uint64_t epoch, uint64_t begin, uint64_t end)
     P.clicks = c->clicks; P.his = c->his; P.masks = c->masks;
     P.begin = (long long)begin; P.end = (long long)end;
     P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed; P.epoch = (unsigned)epoch;
+    set_sampler(c, P);
     P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
     return P;
 }
@@ -441,6 +442,11 @@ int heat_history_indices(heat_ctx *ctx, uint64_t begin, uint64_t end, uint64_t *
 uint64_t heat_philox_draw(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k, uint64_t num_items)
 {
     return philox_draw(seed, (uint32_t)epoch, sample, k, (uint32_t)num_items);
+}
+uint64_t heat_tile_draw(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k, uint64_t num_items, uint64_t tile_size,
+                        uint64_t refresh_interval)
+{
+    return philox_draw(seed, (uint32_t)epoch, sample, k, (uint32_t)num_items, (uint32_t)tile_size, refresh_interval ? refresh_interval : 1);
 }
 
 int heat_eval_dense(heat_ctx *ctx, float *out)

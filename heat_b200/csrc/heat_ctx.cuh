@@ -58,6 +58,14 @@ int fail(const std::string &msg);
             return ::heat::fail(std::string(#expr) + ": " + cudaGetErrorString(_e));             \
     } while (0)
 
+// hot-tile sampler fields of a kernel parameter block from the config (tile_sampler && neg_sampler == 1), else uniform
+template <class Params> inline void set_sampler(const Ctx *c, Params &P)
+{
+    const bool tile = c->cfg.tile_sampler && c->cfg.neg_sampler == 1 && c->cfg.tile_size > 0;
+    P.tile_size = tile ? (unsigned)c->cfg.tile_size : 0u;
+    P.refresh_interval = c->cfg.refresh_interval ? c->cfg.refresh_interval : 1ull;
+}
+
 // train_launch.cu
 int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host);
 // train_bigk.cu

@@ -50,12 +50,35 @@ HEAT_HD Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3
     return o;
 }
 
-HEAT_HD uint32_t philox_draw(uint64_t seed, uint32_t epoch, uint64_t sample, uint32_t k, uint32_t num_items)
+// Hot-tile mode (heat_config.tile_sampler with neg_sampler 1; the reference's RandomTileNegativeSampler::sampling,
+// random_tile_negative_sampler.cpp:22-45 / paper Alg. 1, in stateless form): the samples of one refresh window
+// (global sample index / refresh_interval) draw their negatives from a tile of `tile_size` item ids instead of the
+// whole catalogue, so a window keeps touching the same rows.  Slot j of tile T of an epoch is itself a Philox draw,
+//   item(T, j) = (u64(philox({lo32(T), hi32(T), epoch, j >> 2}, key ^ TILE)[j & 3]) * num_items) >> 32,
+// and a sample's raw 32-bit draw x picks the slot j = (u64(x) * tile_size) >> 32.  tile_size 0 = uniform over all items.
+constexpr uint32_t PHILOX_TILE_KEY0 = 0x656C6974u, PHILOX_TILE_KEY1 = 0x54414548u;   // "tile", "HEAT"
+
+HEAT_HD uint32_t philox_pick(const Philox4 &r, uint32_t k)
+{
+    return (k & 3) == 0 ? r.v[0] : (k & 3) == 1 ? r.v[1] : (k & 3) == 2 ? r.v[2] : r.v[3];
+}
+HEAT_HD uint32_t map_draw(uint32_t x, uint64_t seed, uint32_t epoch, uint64_t sample, uint32_t num_items, uint32_t tile_size,
+                          uint64_t refresh_interval)
+{
+    if (tile_size == 0) return mulhi32(x, num_items);
+    const uint32_t j = mulhi32(x, tile_size);
+    const uint64_t tile = sample / refresh_interval;
+    const Philox4 r = philox4x32_10((uint32_t)tile, (uint32_t)(tile >> 32), epoch, j >> 2,
+                                    (uint32_t)seed ^ PHILOX_TILE_KEY0, (uint32_t)(seed >> 32) ^ PHILOX_TILE_KEY1);
+    return mulhi32(philox_pick(r, j), num_items);
+}
+
+HEAT_HD uint32_t philox_draw(uint64_t seed, uint32_t epoch, uint64_t sample, uint32_t k, uint32_t num_items,
+                             uint32_t tile_size = 0, uint64_t refresh_interval = 1)
 {
     const Philox4 r = philox4x32_10((uint32_t)sample, (uint32_t)(sample >> 32), epoch, k >> 2,
                                     (uint32_t)seed, (uint32_t)(seed >> 32));
-    const uint32_t x = (k & 3) == 0 ? r.v[0] : (k & 3) == 1 ? r.v[1] : (k & 3) == 2 ? r.v[2] : r.v[3];
-    return mulhi32(x, num_items);
+    return map_draw(philox_pick(r, k), seed, epoch, sample, num_items, tile_size, refresh_interval);
 }
 
 }  // namespace heat

@@ -44,6 +44,8 @@ struct TrainParams {
     int no_cache;            // 1: gather the history rows for every sample (history_mode 1)
     int cache_rows;          // train_kernel_bigk.cuh: negative rows kept in shared memory between the two passes
     float lr, lr_w0, clip;
+    unsigned tile_size;                    // hot-tile sampler (philox.cuh): 0 = uniform over all items
+    unsigned long long refresh_interval;   // samples per tile (>= 1)
 };
 
 constexpr unsigned FULL = 0xffffffffu;
@@ -129,7 +131,7 @@ __device__ __forceinline__ int sample_negative(const TrainParams &P, long long s
     long long t = s;
     for (;;) {
         const int d = (int)philox_draw(P.seed, P.epoch, P.sample_offset + (unsigned long long)t, (uint32_t)k,
-                                       (uint32_t)P.num_items);
+                                       (uint32_t)P.num_items, P.tile_size, P.refresh_interval);
         if (d != pos) return d;
         if (t == 0) return 0;
         --t;

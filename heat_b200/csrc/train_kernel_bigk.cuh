@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(BigKCfg<D>::NT, 1) train_bigk_kernel(const Tra
                     for (int t = 0; t < 4; ++t) {
                         const int k = 4 * q + t;
                         if (k < K) {
-                            int d = (int)mulhi32(r.v[t], (uint32_t)P.num_items);
+                            int d = (int)map_draw(r.v[t], P.seed, P.epoch, gs, (uint32_t)P.num_items, P.tile_size, P.refresh_interval);
                             if (d == p) d = sample_negative(P, s, k, p);
                             negid[k] = d;
                             unsigned h = ((unsigned)d * 2654435761u) >> L.hshift;

@@ -163,7 +163,7 @@ __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch
             const int k = 4 * q + t;
             int d = -1 - k;                                // unused slot: a unique negative sentinel
             if (act && k < K) {
-                d = (int)mulhi32(r.v[t], (uint32_t)P.num_items);
+                d = (int)map_draw(r.v[t], P.seed, P.epoch, gs, (uint32_t)P.num_items, P.tile_size, P.refresh_interval);
                 if (d == p) d = sample_negative(P, sj, k, p);
             }
             neg[k] = d;

@@ -132,6 +132,7 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     P.chunk_counter = c->chunk_counter; P.loss_sum = c->loss_sum; P.loss_out = d_loss_out;
     P.begin = (long long)begin; P.end = (long long)end;
     P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed;
+    set_sampler(c, P);
     P.epoch = (unsigned)c->epoch;
     P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
     P.chunk = (int)c->cfg.chunk;

@@ -35,7 +35,8 @@ typedef struct heat_config {
     uint64_t num_users;         /* rows of the (local) user table */
     uint64_t num_items;
     uint64_t train_size;        /* N local samples */
-    uint64_t neg_sampler;       /* 0 uniform, 1 random-tile (same draws in the shipped loop: SURVEY 8.1 a4) */
+    uint64_t neg_sampler;       /* 0 uniform, 1 random-tile: in the reference's shipped loop both draw uniformly
+                                   (SURVEY 8.1 a4), and so they do here unless tile_sampler (below) is set */
     uint64_t tile_size;
     uint64_t refresh_interval;
     uint64_t num_subepochs;     /* fork-only; accepted and ignored */
@@ -70,6 +71,10 @@ typedef struct heat_config {
                                    CTA kernel runs min(#SMs, max(8, num_items/600)) blocks (one sample in flight per
                                    ~600 item rows keeps Recall@20 on the reference's); engines
                                    1 and 2 use one grid over all SMs */
+    uint32_t tile_sampler;      /* 1 with neg_sampler 1: hot-tile policy (random_tile_negative_sampler.cpp:22-45, paper
+                                   Alg. 1): the samples of one window of refresh_interval samples draw their negatives
+                                   from a Philox-defined tile of tile_size item ids (philox.cuh).  0 (default): as the
+                                   reference's shipped loop, the tile is ignored */
 } heat_config;
 
 /* ---- life cycle -------------------------------------------------------------------- */
@@ -151,6 +156,9 @@ int heat_sample_negatives(heat_ctx *ctx, uint64_t epoch, uint64_t begin, uint64_
 int heat_history_indices(heat_ctx *ctx, uint64_t begin, uint64_t end, uint64_t *out_ids, uint64_t *out_count);
 /* Host twin of the sampler (no GPU needed): one raw draw / one slot after look-back. */
 uint64_t heat_philox_draw(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k, uint64_t num_items);
+/* The same with the hot-tile mapping (tile_size 0 = uniform): what the device draws when tile_sampler is on. */
+uint64_t heat_tile_draw(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k, uint64_t num_items,
+                        uint64_t tile_size, uint64_t refresh_interval);
 
 /* ---- evaluation -------------------------------------------------------------------- */
 /* replaces: Engine::evaluate0() + the copying binding lambda (engine.cpp:388-400,

@@ -111,6 +111,8 @@ class COracle(_Base):
             L.heat_oracle_step.restype = C.c_float
             L.heat_oracle_train_epoch.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_int]
             L.heat_oracle_train_epoch.restype = C.c_double
+            L.heat_oracle_neg_table_tile.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, _u64p, C.c_uint64, C.c_uint64, C.c_uint64,
+                                                     C.c_uint64, C.c_uint64, _u64p]
             L.heat_oracle_neg_table.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, _u64p, C.c_uint64,
                                                 C.c_uint64, C.c_uint64, _u64p]
             L.heat_oracle_philox.argtypes = [C.POINTER(C.c_uint32)] * 3
@@ -147,10 +149,15 @@ def philox4x32_10(ctr, key):
     return [int(x) for x in o]
 
 
-def neg_table(seed, epoch, sample_offset, clicks, num_negs, num_items):
-    """[N, K] uint64 negative ids of one epoch under the Philox contract (oracle/philox_ref.h)."""
+def neg_table(seed, epoch, sample_offset, clicks, num_negs, num_items, tile_size=0, refresh_interval=1):
+    """[N, K] uint64 negative ids of one epoch under the Philox contract (oracle/philox_ref.h); tile_size > 0 =
+    the hot-tile mapping."""
     _check(clicks, np.uint64, "clicks")
     out = np.empty((clicks.shape[0], num_negs), np.uint64)
+    if tile_size:
+        COracle.lib().heat_oracle_neg_table_tile(int(seed), int(epoch), int(sample_offset), _p(clicks, _u64p), clicks.shape[0],
+                                                 int(num_negs), int(num_items), int(tile_size), int(refresh_interval), _p(out, _u64p))
+        return out
     COracle.lib().heat_oracle_neg_table(int(seed), int(epoch), int(sample_offset), _p(clicks, _u64p),
                                         clicks.shape[0], int(num_negs), int(num_items), _p(out, _u64p))
     return out

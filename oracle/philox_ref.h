@@ -56,6 +56,41 @@ static inline uint64_t heat_oracle_draw(uint64_t seed, uint64_t epoch,
     return ((uint64_t)r[k & 3] * num_items) >> 32;
 }
 
+/* Hot-tile mode (heat_config.tile_sampler; the reference's RandomTileNegativeSampler::sampling,
+ * random_tile_negative_sampler.cpp:22-45, in stateless form): the samples of one window of
+ * refresh_interval global sample indices draw from a tile of tile_size item ids.
+ *   j    = (u64(r) * tile_size) >> 32                         -- r = the sample's raw 32-bit draw
+ *   T    = sample / refresh_interval
+ *   t    = philox4x32_10({lo32(T), hi32(T), epoch, j >> 2}, {lo32(seed) ^ "tile", hi32(seed) ^ "HEAT"})[j & 3]
+ *   draw = (u64(t) * num_items) >> 32
+ * tile_size 0 = the uniform contract above. */
+static inline uint64_t heat_oracle_draw_tile(uint64_t seed, uint64_t epoch, uint64_t sample, uint32_t k,
+                                             uint64_t num_items, uint64_t tile_size, uint64_t refresh_interval)
+{
+    uint32_t ctr[4] = { (uint32_t)sample, (uint32_t)(sample >> 32), (uint32_t)epoch, k >> 2 };
+    uint32_t key[2] = { (uint32_t)seed, (uint32_t)(seed >> 32) };
+    uint32_t r[4];
+    heat_oracle_philox4x32_10(ctr, key, r);
+    if (tile_size == 0) return ((uint64_t)r[k & 3] * num_items) >> 32;
+    const uint32_t j = (uint32_t)(((uint64_t)r[k & 3] * tile_size) >> 32);
+    const uint64_t T = sample / (refresh_interval ? refresh_interval : 1);
+    uint32_t ctr2[4] = { (uint32_t)T, (uint32_t)(T >> 32), (uint32_t)epoch, j >> 2 };
+    uint32_t key2[2] = { (uint32_t)seed ^ 0x656C6974u, (uint32_t)(seed >> 32) ^ 0x54414548u };
+    heat_oracle_philox4x32_10(ctr2, key2, r);
+    return ((uint64_t)r[j & 3] * num_items) >> 32;
+}
+static inline uint64_t heat_oracle_neg_id_tile(uint64_t seed, uint64_t epoch, uint64_t sample_offset, const uint64_t *clicks,
+                                               uint64_t s, uint32_t k, uint64_t num_items, uint64_t tile_size,
+                                               uint64_t refresh_interval)
+{
+    for (;;) {
+        uint64_t d = heat_oracle_draw_tile(seed, epoch, sample_offset + s, k, num_items, tile_size, refresh_interval);
+        if (d != clicks[2 * s + 1]) return d;
+        if (s == 0) return 0;
+        --s;
+    }
+}
+
 /* Negative id of slot k for local sample s (global index sample_offset + s).
  * clicks is the [N,2] u64 (user, item) array of the local shard. */
 static inline uint64_t heat_oracle_neg_id(uint64_t seed, uint64_t epoch,

@@ -38,3 +38,14 @@ def test_no_cpu_fallback():
         pytest.skip("GPU present")
     with pytest.raises(abi.HeatError, match="no CPU fallback"):
         abi.Context(64, 16, 10, 10)
+
+
+def test_host_tile_sampler_twin_matches_oracle():
+    rng = np.random.default_rng(1)
+    clicks = np.stack([np.arange(300) // 6, rng.integers(0, 500, 300)], 1).astype(np.uint64)
+    for tile, refresh in ((16, 20), (512, 8192), (1, 1)):
+        t = oracle.neg_table(11, 3, 12345, clicks, 8, 500, tile_size=tile, refresh_interval=refresh)
+        tw = np.array([[abi.tile_draw(11, 3, 12345 + s, k, 500, tile, refresh) for k in range(8)] for s in range(300)], dtype=np.uint64)
+        clash = tw == clicks[:, 1:2]
+        assert np.array_equal(t[~clash], tw[~clash])
+    assert abi.tile_draw(11, 3, 99, 5, 500, 0, 1) == abi.philox_draw(11, 3, 99, 5, 500)

@@ -271,3 +271,46 @@ def test_checkpoint_rejects_wrong_shape_and_garbage(tmp_path):
         f.truncate(64 + 100)
     with pytest.raises(abi.HeatError, match="truncated"):
         ctx.load_state(path)
+
+
+TILE = dict(neg_sampler=1, tile_sampler=1, tile_size=32, refresh_interval=50)
+
+
+@pytest.mark.parametrize("engine", [0, 1, 3])
+def test_tile_sampler_indices_bit_exact_and_used_by_every_engine(engine):
+    """SURVEY.md 8.6 row 2 (random_tile_negative_sampler.cpp:22-45 as a hot-tile policy): the device's tile-mode
+    ids equal the oracle's restatement bit for bit, a refresh window only touches its tile, and each training kernel
+    draws exactly those ids (three sequential steps match the oracle fed with them)."""
+    g = load_golden("train_d64_k16")
+    D, K, I = int(g["D"]), int(g["K"]), g["init_item_w"].shape[0]
+    N = g["clicks"].shape[0]
+    off = 777
+    ctx = make_ctx(g, deterministic=True, w0_tail_mode=1, engine=engine, sample_offset=off, **TILE)
+    dev = ctx.sample_negatives(2, 0, N)
+    ref = oracle.neg_table(int(g["seed"]), 2, off, g["clicks"], K, I, tile_size=32, refresh_interval=50)
+    assert np.array_equal(dev, ref)
+    first = 50 - off % 50                                 # local index where the second refresh window starts
+    window = ref[first:first + 50]
+    assert len(set(window.ravel().tolist())) <= 32 + 2    # the tile (+ look-back values from the window before)
+    assert not np.array_equal(ref, oracle.neg_table(int(g["seed"]), 2, off, g["clicks"], K, I))
+    uw, iw, w0 = fresh_tables(g)
+    ctx.bind_tables(uw, iw, w0)
+    negs0 = ctx.sample_negatives(0, 0, 3)
+    _, per = ctx.train_range(0, 3, per_sample=True)
+    ctx.sync_to_host()
+    a = fresh_tables(g)
+    o = oracle.COracle(D, K, g["clicks"], g["his_items"], g["masks"], *a, clip_val=float(g["clip"]), l_r=float(g["lr"]))
+    want = [o.step(int(g["clicks"][s, 0]), int(g["clicks"][s, 1]), negs0[s]) for s in range(3)]
+    o.close()
+    assert np.allclose(per, want, rtol=2e-3, atol=1e-5), (per, want)
+    assert rel_err(uw, a[0]) < 2e-4 and rel_err(iw, a[1]) < 2e-4
+    ctx.close()
+
+
+def test_neg_sampler_1_without_tile_sampler_draws_uniformly():
+    """The reference's shipped loop calls ignore_pos_sampling, which ignores the tile: neg_sampler 1
+    alone must not change a single id."""
+    g = load_golden("train_d64_k16")
+    K, I, N = int(g["K"]), g["init_item_w"].shape[0], g["clicks"].shape[0]
+    ctx = make_ctx(g, neg_sampler=1, tile_size=32, refresh_interval=50)
+    assert np.array_equal(ctx.sample_negatives(0, 0, N), oracle.neg_table(int(g["seed"]), 0, 0, g["clicks"], K, I))
