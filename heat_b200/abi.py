@@ -29,7 +29,7 @@ SYMBOLS = [
     "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
-    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw",
+    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw", "heat_last_engine",
 ]
 
 
@@ -85,6 +85,7 @@ def lib():
         L.heat_last_eval_ms.argtypes = [C.c_void_p, _f32p]
         L.heat_last_epoch_ms.argtypes = [C.c_void_p, _f32p]
         L.heat_launch_count.argtypes = [C.c_void_p, _u64p]
+        L.heat_last_engine.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         L.heat_sample_negatives.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, _u64p]
         L.heat_history_indices.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _u64p, _u64p]
         L.heat_philox_draw.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64]
@@ -265,6 +266,9 @@ class Context:
 
     def last_eval_ms(self):
         v = C.c_float(); _ck(lib().heat_last_eval_ms(self._h, C.byref(v))); return v.value
+
+    def last_engine(self):
+        v = C.c_int(); _ck(lib().heat_last_engine(self._h, C.byref(v))); return v.value
 
     def launch_count(self):
         v = C.c_uint64(); _ck(lib().heat_launch_count(self._h, C.byref(v))); return v.value

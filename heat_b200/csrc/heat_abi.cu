@@ -392,6 +392,7 @@ int heat_set_epoch(heat_ctx *ctx, uint64_t epoch) { Ctx *c = reinterpret_cast<Ct
 int heat_last_kernel_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_kernel_ms; return 0; }
 int heat_last_epoch_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_epoch_ms; return 0; }
 int heat_last_eval_ms(heat_ctx *ctx, float *ms) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !ms) return fail("null argument"); *ms = c->last_eval_ms; return 0; }
+int heat_last_engine(heat_ctx *ctx, int *engine) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !engine) return fail("null argument"); *engine = c->last_engine; return 0; }
 int heat_launch_count(heat_ctx *ctx, uint64_t *n) { Ctx *c = reinterpret_cast<Ctx *>(ctx); if (!c || !n) return fail("null argument"); *n = c->launches; return 0; }
 
 int heat_sample_negatives(heat_ctx *ctx, uint64_t epoch, uint64_t begin, uint64_t end, uint64_t *out)

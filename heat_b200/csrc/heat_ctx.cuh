@@ -35,6 +35,7 @@ struct Ctx {
     uint64_t epoch = 0;
     float last_kernel_ms = 0.f, last_eval_ms = 0.f, last_epoch_ms = 0.f;
     uint64_t launches = 0;
+    int last_engine = 0;      // kernel family of the last training launch: 1 warp per sample, 2 CTA per sample, 3 large-negative
 
     // multi-GPU
     int rank = 0, world = 1;

@@ -64,10 +64,10 @@ int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
 
 // Pick the instantiation for (D, K, warps).  K must fit the register-resident path:
 // K <= NJ * 32/(D/4).
-int dispatch(Ctx *c, const TrainParams &P, bool deterministic)
+int dispatch(Ctx *c, const TrainParams &P, bool deterministic, int warps_override = 0)
 {
     const int D = (int)c->cfg.emb_dim, K = P.K;
-    int warps = (int)c->cfg.warps_per_block;
+    int warps = warps_override ? warps_override : (int)c->cfg.warps_per_block;
     const int bps = c->cfg.blocks_per_sm ? (int)c->cfg.blocks_per_sm : 1;
     int blocks = deterministic ? 1 : c->num_sms * bps;
     if (c->cfg.max_blocks && blocks > (int)c->cfg.max_blocks) blocks = (int)c->cfg.max_blocks;
@@ -110,6 +110,24 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic)
                 "): the warp-per-sample kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16 (engine 0 or 3 covers the rest)");
 }
 
+// engine 0 (auto): the parity budget is about one sample in flight per 600 item rows.  The
+// CTA kernel spends it on <= #SMs samples with the shortest latency; once the item table is large enough for the
+// budget to cover a whole grid of the warp-per-sample kernel (#SMs x warps), that kernel's ~2x higher throughput
+// is parity-safe too (measured on the 2 M-item shard of BASELINE configs[4]: epoch losses within 0.01 of the CTA
+// kernel's at twice the samples/s).  Returns the warps per block to run it with, 0 = stay on the CTA kernel.
+int auto_warp_engine(const Ctx *c, int D, int K)
+{
+    if (!warp_covers(D, K) || c->cfg.deterministic || c->cfg.max_blocks || c->cfg.warps_per_block || c->cfg.blocks_per_sm) return 0;
+    const uint64_t budget = c->cfg.num_items / 600, sms = (uint64_t)c->num_sms;
+    if (D == 64 && K <= 16) {
+        if (budget >= sms * 12) return 12;
+        if (budget >= sms * 8) return 8;      // 8 warps x 148 in flight at ~8 us per sample still beats 148 CTAs at 1.5 us
+        return 0;
+    }
+    const uint64_t w = D == 128 ? 4 : 8;      // the fixed block shapes of the other instantiations
+    return budget >= sms * w ? (int)w : 0;
+}
+
 }  // namespace
 
 int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host)
@@ -142,12 +160,15 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
 
     P.no_cache = c->cfg.history_mode == 1;
     int rc = -1;
-    if (c->cfg.engine != 1 && c->cfg.engine != 3) rc = dispatch_cta(c, P, c->cfg.deterministic != 0);      // 0 auto, 2 forced
+    c->last_engine = 0;
+    const int auto_w = c->cfg.engine == 0 ? auto_warp_engine(c, (int)c->cfg.emb_dim, P.K) : 0;
+    if (auto_w) { rc = dispatch(c, P, false, auto_w); c->last_engine = 1; }
+    else if (c->cfg.engine != 1 && c->cfg.engine != 3) { rc = dispatch_cta(c, P, c->cfg.deterministic != 0); c->last_engine = 2; }      // 0 auto, 2 forced
     if (rc == -1 && c->cfg.engine == 2) rc = fail("engine 2 (CTA per sample) does not cover this (emb_dim, num_negs)");
     if (rc == -1) {
         const bool det = c->cfg.deterministic != 0;
-        if (c->cfg.engine == 3 || (c->cfg.engine == 0 && !warp_covers((int)c->cfg.emb_dim, P.K))) rc = dispatch_bigk(c, P, det);
-        else rc = dispatch(c, P, det);
+        if (c->cfg.engine == 3 || (c->cfg.engine == 0 && !warp_covers((int)c->cfg.emb_dim, P.K))) { rc = dispatch_bigk(c, P, det); c->last_engine = 3; }
+        else { rc = dispatch(c, P, det); c->last_engine = 1; }
     }
     if (rc == 0) {
         double loss = 0.0;

@@ -64,7 +64,7 @@ typedef struct heat_config {
     uint32_t history_mode;      /* 0 default: the history column sums are gathered once per run of a user's
                                    consecutive samples and patched with the exact change of the rows the warp
                                    rewrites; 1: re-gathered for every sample (the reference's literal sequence) */
-    uint32_t engine;            /* 0 auto; 1 warp-per-sample kernel (train_kernel.cuh: highest throughput, thousands of
+    uint32_t engine;            /* 0 auto (see heat_last_engine); 1 warp-per-sample kernel (train_kernel.cuh: highest throughput, thousands of
                                    samples in flight); 2 CTA-per-sample kernel (train_kernel_cta.cuh: lowest latency per
                                    sample, one sample in flight per thread block -- the default where it applies) */
     uint32_t max_blocks;        /* cap on thread blocks = bound on Hogwild concurrency.  0 = default: with engine 0 the
@@ -121,6 +121,11 @@ int heat_set_epoch(heat_ctx *ctx, uint64_t epoch);
 int heat_last_kernel_ms(heat_ctx *ctx, float *ms);
 /* device time of the whole last heat_train_epoch (kernel(s), zero_grad, item syncs), CUDA events, ms */
 int heat_last_epoch_ms(heat_ctx *ctx, float *ms);
+/* kernel family the last heat_train_epoch / heat_train_range ran: 1 warp-per-sample (train_kernel.cuh), 2 CTA-per-sample
+ * (train_kernel_cta.cuh), 3 large-negative (train_kernel_bigk.cuh); 0 before the first launch.  With engine 0 the
+ * library picks: large num_negs -> 3; an item table large enough for the parity budget of one sample in flight per
+ * ~600 item rows to cover a full grid of warps (>= ~1.07 M items at D=64, K<=16) -> 1; otherwise 2. */
+int heat_last_engine(heat_ctx *ctx, int *engine);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 int heat_launch_count(heat_ctx *ctx, uint64_t *n);
 

@@ -314,3 +314,37 @@ def test_neg_sampler_1_without_tile_sampler_draws_uniformly():
     K, I, N = int(g["K"]), g["init_item_w"].shape[0], g["clicks"].shape[0]
     ctx = make_ctx(g, neg_sampler=1, tile_size=32, refresh_interval=50)
     assert np.array_equal(ctx.sample_negatives(0, 0, N), oracle.neg_table(int(g["seed"]), 0, 0, g["clicks"], K, I))
+
+
+def test_auto_engine_follows_the_parity_budget():
+    """engine 0: CTA kernel while the budget of one sample in flight per ~600 item rows is below a full grid of
+    warps, the warp-per-sample kernel once the item table is large enough, the large-negative kernel for big K."""
+    import torch
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    rng = np.random.default_rng(0)
+    U, D, N, H = 64, 64, 4096, 100
+
+    def engine_for(I, K=16, **kw):
+        clicks = np.stack([np.sort(rng.integers(0, U, N)), rng.integers(0, I, N)], 1).astype(np.uint64)
+        his = rng.integers(0, I, (U, H)).astype(np.uint64)
+        masks = np.full((U, 1), H, np.uint64)
+        ctx = abi.Context(D, K, U, I, **kw)
+        ctx.set_dataset(clicks, his, masks)
+        uw = (rng.standard_normal((U, D)) * 1e-2).astype(np.float32)
+        iw = np.full((I, D), 1e-2, np.float32)
+        ctx.bind_tables(uw, iw, (rng.standard_normal((D, D)) * 1e-2).astype(np.float32))
+        assert ctx.last_engine() == 0
+        loss = ctx.train_epoch()
+        e = ctx.last_engine()
+        ctx.close()
+        assert np.isfinite(loss)
+        return e
+
+    assert engine_for(40000) == 2
+    assert engine_for(sms * 8 * 600 - 600) == 2
+    assert engine_for(sms * 8 * 600) == 1
+    assert engine_for(sms * 12 * 600) == 1
+    assert engine_for(sms * 12 * 600, max_blocks=32) == 2          # an explicit concurrency bound keeps the CTA kernel
+    assert engine_for(sms * 12 * 600, engine=2) == 2
+    assert engine_for(40000, engine=1) == 1
+    assert engine_for(40000, K=200) == 3
