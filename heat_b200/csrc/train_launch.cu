@@ -110,15 +110,18 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic, int warps_overrid
                 "): the warp-per-sample kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16 (engine 0 or 3 covers the rest)");
 }
 
-// engine 0 (auto): the parity budget is about one sample in flight per 600 item rows.  The
-// CTA kernel spends it on <= #SMs samples with the shortest latency; once the item table is large enough for the
-// budget to cover a whole grid of the warp-per-sample kernel (#SMs x warps), that kernel's ~2x higher throughput
-// is parity-safe too (measured on the 2 M-item shard of BASELINE configs[4]: epoch losses within 0.01 of the CTA
-// kernel's at twice the samples/s).  Returns the warps per block to run it with, 0 = stay on the CTA kernel.
+// engine 0 (auto): the CTA kernel keeps the reference's loss / Recall with one sample in flight per ~600 item rows
+//  and spends that budget on <= #SMs samples with the shortest latency.  The warp-per-sample
+// kernel holds a sample ~5x longer between its reads and its writes, so it needs ~1100 item rows per sample in flight
+// for the same per-epoch loss tolerance (profiles/r01_recall_parity.md: at 620-630 rows per sample its Recall@20 is
+// within 0.0002 of the reference but its first epochs' losses are 0.05-0.06 above; at 1126 rows per sample -- the 2 M-item
+// shard of BASELINE configs[4] -- its epoch losses are within 0.01 of the CTA kernel's at twice the samples/s).  Once the
+// item table is large enough for a whole grid of it (#SMs x warps) that kernel is the faster parity-safe choice.
+// Returns the warps per block to run it with, 0 = stay on the CTA kernel.
 int auto_warp_engine(const Ctx *c, int D, int K)
 {
     if (!warp_covers(D, K) || c->cfg.deterministic || c->cfg.max_blocks || c->cfg.warps_per_block || c->cfg.blocks_per_sm) return 0;
-    const uint64_t budget = c->cfg.num_items / 600, sms = (uint64_t)c->num_sms;
+    const uint64_t budget = c->cfg.num_items / 1100, sms = (uint64_t)c->num_sms;
     if (D == 64 && K <= 16) {
         if (budget >= sms * 12) return 12;
         if (budget >= sms * 8) return 8;      // 8 warps x 148 in flight at ~8 us per sample still beats 148 CTAs at 1.5 us

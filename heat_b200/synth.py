@@ -23,6 +23,10 @@ SHAPES = {
     "gowalla": (29858, 40981, 810128),
     "yelp18": (31668, 38048, 1237259),
     "amazon-book": (52643, 91599, 2380730),
+    # large catalogues (sparser than the LightGCN sets): the parity budget of one sample in flight per ~600 item rows
+    # reaches a grid of the warp-per-sample kernel here (train_launch.cu: auto_warp_engine) -- 8 resp. 12 warps per SM
+    "wide-750k": (100000, 750000, 5000000),
+    "wide-1100k": (100000, 1100000, 5000000),
     "tiny": (200, 300, 4000),
     "small": (2000, 3000, 60000),
 }

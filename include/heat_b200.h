@@ -123,8 +123,8 @@ int heat_last_kernel_ms(heat_ctx *ctx, float *ms);
 int heat_last_epoch_ms(heat_ctx *ctx, float *ms);
 /* kernel family the last heat_train_epoch / heat_train_range ran: 1 warp-per-sample (train_kernel.cuh), 2 CTA-per-sample
  * (train_kernel_cta.cuh), 3 large-negative (train_kernel_bigk.cuh); 0 before the first launch.  With engine 0 the
- * library picks: large num_negs -> 3; an item table large enough for the parity budget of one sample in flight per
- * ~600 item rows to cover a full grid of warps (>= ~1.07 M items at D=64, K<=16) -> 1; otherwise 2. */
+ * library picks: large num_negs -> 3; an item table large enough for a full grid of warps at one sample in flight per
+ * ~1100 item rows (>= 1.30 M items for 8 warps per SM, >= 1.95 M for 12, at D=64, K<=16) -> 1; otherwise 2. */
 int heat_last_engine(heat_ctx *ctx, int *engine);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 int heat_launch_count(heat_ctx *ctx, uint64_t *n);

@@ -341,10 +341,10 @@ def test_auto_engine_follows_the_parity_budget():
         return e
 
     assert engine_for(40000) == 2
-    assert engine_for(sms * 8 * 600 - 600) == 2
-    assert engine_for(sms * 8 * 600) == 1
-    assert engine_for(sms * 12 * 600) == 1
-    assert engine_for(sms * 12 * 600, max_blocks=32) == 2          # an explicit concurrency bound keeps the CTA kernel
-    assert engine_for(sms * 12 * 600, engine=2) == 2
+    assert engine_for(sms * 8 * 1100 - 1100) == 2
+    assert engine_for(sms * 8 * 1100) == 1
+    assert engine_for(sms * 12 * 1100) == 1
+    assert engine_for(sms * 12 * 1100, max_blocks=32) == 2         # an explicit concurrency bound keeps the CTA kernel
+    assert engine_for(sms * 12 * 1100, engine=2) == 2
     assert engine_for(40000, engine=1) == 1
     assert engine_for(40000, K=200) == 3
