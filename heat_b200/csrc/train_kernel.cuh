@@ -139,6 +139,19 @@ __device__ __forceinline__ int sample_negative(const TrainParams &P, long long s
     }
 }
 
+// max(x, eps)^-1/2 (matrix_factorization.cpp:50-53 clamps the squared norms at eps before the root)
+// as MUFU.RSQ + one Newton step (full fp32 accuracy without the division / square-root subroutines)
+__device__ __forceinline__ float rsqrt_eps(float x)
+{
+    x = fmaxf(x, 1e-8f);
+    const float y = rsqrtf(x);
+    return y * fmaf(-0.5f * x * y, y, 1.5f);
+}
+
+// Two 11-bit hashes of an item id: the bit positions of the per-warp 2048-bit history filter (CACHE)
+__device__ __forceinline__ unsigned hfilter_h1(int id) { return ((unsigned)id * 0x9E3779B1u) >> 21; }
+__device__ __forceinline__ unsigned hfilter_h2(int id) { return ((unsigned)id * 0x85EBCA77u + 0x165667B1u) >> 21; }
+
 // History ids of user u: lane holds ids lane, lane+32, lane+64, lane+96 (max_his <= 128).
 __device__ __forceinline__ void load_history_ids(const TrainParams &P, int u, int lane, int (&hid)[4])
 {
@@ -209,6 +222,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane / VL, sl = lane % VL;
     float *ring = smem + D * D + warp * (32 * 2 * D);
+    unsigned *hfilter = reinterpret_cast<unsigned *>(smem + D * D + WARPS * (32 * 2 * D)) + warp * 64;   // CACHE: 2048-bit filter
 
     for (int i = threadIdx.x * 4; i < D * D; i += WARPS * 32 * 4)
         *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
@@ -216,7 +230,6 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
 
     const float gamma = 0.4f;                        // behavior_aggregators.cpp:37
     const float omg = 1.0f - gamma;
-    const float eps = 1e-8f;                         // matrix_factorization.cpp:54
     const float score_mul = (float)(1.0 / 0.07);     // matrix_factorization.cpp:101
     const int K = P.K;
     unsigned iter = 0;                               // BehaviorAggregator::iteration of this warp
@@ -231,6 +244,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
     // warps during the run are seen at the next gather instead of at the next sample.
     constexpr int REGATHER = 64;
     int cur_u = -1, H = 0, age = 0;
+    int hid[4] = {0, 0, 0, 0};                       // the run's history ids: lane holds positions lane + 32q
     float4 acc = f4zero(), u_keep = f4zero(), gu_keep = f4zero();
 
     for (;;) {
@@ -278,8 +292,20 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             // ---- history aggregation (behavior_aggregators.cpp:60-105)
             if (fresh) {
                 H = __ldg(P.masks + u);
-                int hid[4];
                 load_history_ids(P, u, lane, hid);
+                if (CACHE) {                                   // the run's history as a Bloom filter (two probes per id)
+                    hfilter[lane] = 0u; hfilter[lane + 32] = 0u;
+                    __syncwarp();
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (lane + 32 * q < H) {
+                            const unsigned a = hfilter_h1(hid[q]), b = hfilter_h2(hid[q]);
+                            atomicOr(&hfilter[a >> 5], 1u << (a & 31));
+                            atomicOr(&hfilter[b >> 5], 1u << (b & 31));
+                        }
+                    }
+                    __syncwarp();
+                }
                 acc = f4zero();
                 for (int h0 = 0; h0 < H; h0 += R * UNR) {
                     const int hq = pick4(hid, h0 >> 5);
@@ -301,22 +327,27 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             int pmult = 0;
             bool regather = false;
             if (CACHE) {
-                constexpr int NPASS = (NJ * R + 15) / 16;
-                const int *hrow = P.his + (size_t)u * P.max_his;
-                bool nhit = false;
-                for (int c0 = 0; c0 < H; c0 += 16) {
-                    const int hi = c0 + lane - 16;
-                    const int hv = (lane >= 16 && hi < H) ? __ldg(hrow + hi) : (-64 - lane);
-                    pmult += __popc(__ballot_sync(FULL, hv == p));
+                // the ids sit in registers since the run's gather: the positive's multiplicity is four ballots; the
+                // negatives go through the filter first (two shared-memory probes per lane) and only a sample with a
+                // filter hit (~7 % at H = 68) pays the exact comparison against the 128 register-resident ids
 #pragma unroll
-                    for (int ps = 0; ps < NPASS; ++ps) {
-                        const int nv = __shfl_sync(FULL, negid, (ps * 16 + (lane & 15)) & 31);
-                        const unsigned mm = __match_any_sync(FULL, lane < 16 ? nv : hv);
-                        nhit |= (lane < 16) && (mm >> 16) != 0;
+                for (int q = 0; q < 4; ++q) pmult += __popc(__ballot_sync(FULL, lane + 32 * q < H && hid[q] == p));
+                bool maybe = false;
+                if (lane < K) {
+                    const unsigned a = hfilter_h1(negid), b = hfilter_h2(negid);
+                    maybe = ((hfilter[a >> 5] >> (a & 31)) & (hfilter[b >> 5] >> (b & 31)) & 1u) != 0;
+                }
+                bool nhit = false;
+                if (__any_sync(FULL, maybe)) {
+                    for (int k = 0; k < K; ++k) {
+                        const int nk = __shfl_sync(FULL, negid, k);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) nhit |= lane + 32 * q < H && hid[q] == nk;
                     }
+                    nhit = __any_sync(FULL, nhit);
                 }
                 const bool pin = __any_sync(FULL, negid == p);
-                regather = __any_sync(FULL, nhit) || (pmult != 0 && (dup || pin));
+                regather = nhit || (pmult != 0 && (dup || pin));
             }
             const float rH = (float)(1.0 / (double)H);     // behavior_aggregators.cpp:63
             const float4 mean = rH * acc;
@@ -343,22 +374,23 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             const float uu = group_sum<VL>(dot4(ua, ua));
             const float pp = group_sum<VL>(dot4(pw, pw));
             const float upd = group_sum<VL>(dot4(ua, pw));
-            const float unorm = sqrtf(fmaxf(uu, eps)), pnorm = sqrtf(fmaxf(pp, eps));
-            const float unorm3 = unorm * unorm * unorm, pnorm3 = pnorm * pnorm * pnorm;
-            const float r_u3_p = 1.f / (unorm3 * pnorm), r_u_p3 = 1.f / (unorm * pnorm3);
+            //      1/|x| = max(x.x, eps)^-1/2 as MUFU.RSQ + one Newton step: the products below replace the reference's
+            //      sqrt / divide sequence at fp32 accuracy (the single-step parity tests hold at 1e-5)
+            const float ru = rsqrt_eps(uu), rp = rsqrt_eps(pp);
+            const float r_u3_p = (ru * ru) * (ru * rp), r_u_p3 = (ru * rp) * (rp * rp);
             const float4 gu_p = r_u3_p * (uu * pw - upd * ua);
             const float4 gp_p = (-r_u_p3) * (pp * ua - upd * pw);
-            const float cos_p = upd / (unorm * pnorm);
+            const float cos_p = upd * (ru * rp);
 
             // ---- negatives: dots, scores, softmax loss (matrix_factorization.cpp:82-109)
-            float un[NJ], nn[NJ], nnorm[NJ], sc[NJ];
+            float un[NJ], nn[NJ], rn[NJ], sc[NJ];
             float m = -INFINITY;
 #pragma unroll
             for (int j = 0; j < NJ; ++j) {
                 un[j] = group_sum<VL>(dot4(ua, nw[j]));
                 nn[j] = group_sum<VL>(dot4(nw[j], nw[j]));
-                nnorm[j] = sqrtf(nn[j] < eps ? eps : nn[j]);
-                sc[j] = (j * R + g < K) ? (un[j] / (unorm * nnorm[j]) - cos_p) * score_mul : -INFINITY;
+                rn[j] = rsqrt_eps(nn[j]);
+                sc[j] = (j * R + g < K) ? (un[j] * (ru * rn[j]) - cos_p) * score_mul : -INFINITY;
                 m = fmaxf(m, sc[j]);
             }
             m = cross_max<VL>(m);
@@ -380,8 +412,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
                     if (UPD == UPD_FRESH) dl[j] = f4zero();
                     if (j * R + g < K) {
                         const float lg = (sc[j] * inv_esum) * score_mul;            // :109
-                        const float nnorm3 = nnorm[j] * nnorm[j] * nnorm[j];
-                        const float r_u3_n = 1.f / (unorm3 * nnorm[j]), r_u_n3 = 1.f / (unorm * nnorm3);
+                        const float r_u3_n = (ru * ru) * (ru * rn[j]), r_u_n3 = (ru * rn[j]) * (rn[j] * rn[j]);
                         const float4 gu_n = r_u3_n * (uu * nw[j] - un[j] * ua);     // :138
                         const float4 gn_n = r_u_n3 * (nn[j] * ua - un[j] * nw[j]);  // :139
                         fma4(gacc, lg, gu_n - gu_p);                                 // :141
@@ -436,8 +467,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
                     for (int gg = 0; gg < R; ++gg) {
                         if (gg == g && j * R + g < K) {
                             const float lg = (sc[j] * inv_esum) * score_mul;
-                            const float nnorm3 = nnorm[j] * nnorm[j] * nnorm[j];
-                            const float r_u3_n = 1.f / (unorm3 * nnorm[j]), r_u_n3 = 1.f / (unorm * nnorm3);
+                            const float r_u3_n = (ru * ru) * (ru * rn[j]), r_u_n3 = (ru * rn[j]) * (rn[j] * rn[j]);
                             const float4 gu_n = r_u3_n * (uu * nw[j] - un[j] * ua);
                             const float4 gn_n = r_u_n3 * (nn[j] * ua - un[j] * nw[j]);
                             fma4(gacc, lg, gu_n - gu_p);

@@ -94,15 +94,6 @@ template <int VL, int N> __device__ __forceinline__ void group_sum_n(float (&v)[
     }
 }
 
-// max(x, eps)^-1/2 (matrix_factorization.cpp:50-53 clamps the squared norms at eps before the root)
-// as MUFU.RSQ + one Newton step (full fp32 accuracy without the division / square-root subroutines)
-__device__ __forceinline__ float rsqrt_eps(float x)
-{
-    x = fmaxf(x, 1e-8f);
-    const float y = rsqrtf(x);
-    return y * fmaf(-0.5f * x * y, y, 1.5f);
-}
-
 // 16-byte asynchronous copy global -> shared (LDGSTS, L2-coherent): the row prefetch.  Every thread copies
 // exactly the slice it consumes later, so completion needs no cross-thread synchronisation.
 __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gsrc)

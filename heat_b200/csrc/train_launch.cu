@@ -12,7 +12,7 @@ template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD = UPD_STORE, bool CA
 int launch_one(Ctx *c, const TrainParams &P, int blocks)
 {
     auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G, UPD, CACHE>;
-    const size_t smem = (size_t)(D * D + WARPS * 32 * 2 * D) * sizeof(float);
+    const size_t smem = (size_t)(D * D + WARPS * 32 * 2 * D) * sizeof(float) + (size_t)WARPS * 64 * sizeof(unsigned);   // W0, rings, history filters
     HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
     kern<<<blocks, WARPS * 32, smem, c->stream>>>(P);

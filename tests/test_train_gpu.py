@@ -49,7 +49,7 @@ def test_history_gather_indices_bit_exact(name):
 
 # engine 0 = the default for the shape (large num_negs -> train_kernel_bigk.cuh); engine 3 forces the
 # large-negative kernel onto the small shapes too
-ENGINE_CASES = [(n, 0) for n in TRAIN_CASES + BIGK_CASES] + [(n, 3) for n in TRAIN_CASES]
+ENGINE_CASES = [(n, 0) for n in TRAIN_CASES + BIGK_CASES] + [(n, 3) for n in TRAIN_CASES] + [(n, 1) for n in TRAIN_CASES]
 
 
 @pytest.mark.parametrize("name,engine", ENGINE_CASES)
