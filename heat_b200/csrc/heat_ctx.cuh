@@ -69,8 +69,10 @@ template <class Params> inline void set_sampler(const Ctx *c, Params &P)
 
 // train_launch.cu
 int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host);
-// train_bigk.cu
+// train_launch_tile.cu: the CTA kernel's hot-tile-sampler instantiations (-1: (emb_dim, num_negs) not covered)
 struct TrainParams;
+int dispatch_cta_tile(Ctx *c, const TrainParams &P, int blocks);
+// train_bigk.cu
 int dispatch_bigk(Ctx *c, const TrainParams &P, bool deterministic);
 // eval_kernel.cu
 int eval_dense(Ctx *c, float *out_host);

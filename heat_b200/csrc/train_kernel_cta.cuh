@@ -113,7 +113,7 @@ template <int NPS> struct CtaCtrl {
 
 // Control warp: prepare up to 32 consecutive samples of this CTA's current chunk, one LANE per sample
 // (fetches the next chunk when the current one is used up; cnt = 0 when there is none).
-template <int D, int NPS>
+template <int D, int NPS, bool TILE>
 __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch<NPS> *B, int lane, CtaCtrl<NPS> &c,
                                                   long long nchunks, bool no_cache)
 {
@@ -154,7 +154,7 @@ __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch
             const int k = 4 * q + t;
             int d = -1 - k;                                // unused slot: a unique negative sentinel
             if (act && k < K) {
-                d = (int)map_draw(r.v[t], P.seed, P.epoch, gs, (uint32_t)P.num_items, P.tile_size, P.refresh_interval);
+                d = (int)map_draw(r.v[t], P.seed, P.epoch, gs, (uint32_t)P.num_items, TILE ? P.tile_size : 0u, P.refresh_interval);
                 if (d == p) d = sample_negative(P, sj, k, p);
             }
             neg[k] = d;
@@ -224,7 +224,8 @@ __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch
 #define HEAT_PT(i) do { } while (0)
 #endif
 
-template <int D, int NPS>
+// TILE: the hot-tile sampler (philox.cuh) is compiled in; the default instantiation carries none of its code
+template <int D, int NPS, bool TILE = false>
 __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const TrainParams P)
 {
     using C = CtaCfg<D, NPS>;
@@ -250,7 +251,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 if (lane == 0) ring[slot_].cnt = 0;
                 return false;
             }
-            cta_prepare_batch<D, NPS>(P, &ring[slot_], lane, ctl, nchunks, no_cache);
+            cta_prepare_batch<D, NPS, TILE>(P, &ring[slot_], lane, ctl, nchunks, no_cache);
             __syncwarp();
             return ring[slot_].cnt != 0;
         };

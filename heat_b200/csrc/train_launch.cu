@@ -54,6 +54,7 @@ int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
         const int cap = (int)std::max<uint64_t>(8, c->cfg.num_items / 600);
         if (blocks > cap) blocks = cap;
     }
+    if (P.tile_size != 0) return dispatch_cta_tile(c, P, blocks);       // hot-tile sampler: train_launch_tile.cu
     if (D == 64 && K <= 16) return launch_cta<64, 1>(c, P, blocks);
     if (D == 64 && K <= 32) return launch_cta<64, 2>(c, P, blocks);
     if (D == 64 && K <= 64) return launch_cta<64, 4>(c, P, blocks);
