@@ -226,6 +226,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         dist.broadcast(uid, 0)
         ctx.comm_init(rank, world, uid.cpu().numpy())
         ctx.set_sync_interval(args.sync_interval)
+    exchange = {0: None, 1: "NCCL all-reduce of the item/W0 delta", 2: "fused peer-memory exchange kernel (CUDA IPC over NVLink)"}[ctx.comm_mode()]
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -373,7 +374,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                     "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "what": "heat_set_dataset + heat_upload_tables + heat_train_epoch + heat_sync_to_host from pinned host buffers"},
             "roofline": roofline, "loss_first_last": [losses[0], losses[-1]], "wall_s_timed_region": wall,
-            "update_mode": args.update_mode, "sync_interval": args.sync_interval if world > 1 else None,
+            "update_mode": args.update_mode, "sync_interval": args.sync_interval if world > 1 else None, "exchange": exchange,
             "engine": {0: "auto: CTA-per-sample kernel, parity-grade concurrency", 1: "warp-per-sample kernel, full grid",
                        2: "CTA-per-sample kernel"}[args.engine]}
     if ev is not None:

@@ -29,7 +29,7 @@ SYMBOLS = [
     "heat_last_kernel_ms", "heat_last_epoch_ms", "heat_launch_count", "heat_sample_negatives", "heat_history_indices",
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
-    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw", "heat_last_engine",
+    "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw", "heat_last_engine", "heat_comm_mode",
 ]
 
 
@@ -44,7 +44,7 @@ class HeatConfig(C.Structure):
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
         ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
         ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("engine", C.c_uint32), ("max_blocks", C.c_uint32),
-        ("tile_sampler", C.c_uint32),
+        ("exchange_mode", C.c_uint32), ("tile_sampler", C.c_uint32),
     ]
 
 
@@ -98,6 +98,7 @@ def lib():
         L.heat_comm_unique_id.argtypes = [_u8p]
         L.heat_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, _u8p]
         L.heat_comm_sync_items.argtypes = [C.c_void_p]
+        L.heat_comm_mode.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         L.heat_set_sync_interval.argtypes = [C.c_void_p, C.c_uint64]
         L.heat_comm_allreduce_f64.argtypes = [C.c_void_p, _f64p, C.c_int]
         L.heat_probe_l2_bandwidth.argtypes = [C.c_int, C.c_uint64, C.c_int, _f64p]
@@ -172,7 +173,7 @@ class Context:
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
                  warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, history_mode=0, engine=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
-                 tile_sampler=0, device=0):
+                 tile_sampler=0, exchange_mode=0, device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
                          train_size=0, neg_sampler=neg_sampler, tile_size=tile_size,
@@ -181,7 +182,8 @@ class Context:
                          sample_offset=sample_offset, chunk=chunk, deterministic=int(bool(deterministic)),
                          w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
                          max_blocks=max_blocks, update_mode=update_mode,
-                         sync_average=sync_average, history_mode=history_mode, engine=engine, tile_sampler=tile_sampler)
+                         sync_average=sync_average, history_mode=history_mode, engine=engine, tile_sampler=tile_sampler,
+                         exchange_mode=exchange_mode)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0
@@ -318,6 +320,10 @@ class Context:
     def comm_init(self, rank, world, uid):
         uid = np.ascontiguousarray(uid, np.uint8)
         _ck(lib().heat_comm_init(self._h, rank, world, _ptr(uid, _u8p)))
+
+    def comm_mode(self):
+        """0 no communicator, 1 NCCL all-reduce, 2 fused peer-memory exchange kernel."""
+        v = C.c_int(); _ck(lib().heat_comm_mode(self._h, C.byref(v))); return v.value
 
     def comm_sync_items(self):
         _ck(lib().heat_comm_sync_items(self._h))

@@ -8,11 +8,22 @@
 // This replaces the fork's per-row MPI_Bcast / MPI_Allreduce of item rows and its W0 average
 // (train/engine.cpp:148-152, 262-286, 354-375).  Item grad rows stay local to a rank.
 //
+// Exchange kernel (default): the all-reduce is not a library call between two elementwise kernels but ONE kernel per
+// rank over NVLink peer memory (`peer_sync_kernel`): every rank maps every other rank's item table, base copy and W0
+// through CUDA IPC at heat_comm_init; rank r owns a 1/world slice of the rows, reads that slice of every replica
+// straight from the peers' HBM (system-scope loads), forms base + scale * sum_q (w_q - base) in rank order (so all
+// replicas receive the same bits) and stores the result into every replica's table and base copy.  Two flag
+// barriers in peer memory bracket it (all ranks' training stores done / all remote stores landed).  Per rank that is
+// (world-1)/world of the table read and 2(world-1)/world written over NVLink instead of a delta kernel, a ring
+// all-reduce and an apply kernel (three passes over HBM plus the ring's 2(world-1)/world).  NCCL remains the
+// bootstrap (handle all-gather), the scalar reductions, and the fallback when peer mapping is unavailable.
+//
 // NCCL is resolved at run time (dlopen "libnccl.so.2"): inside a PyTorch process that is the
 // library torch already loaded, so both share one NCCL; in a plain C++ host it is the system one.
 #include <dlfcn.h>
 #include <nccl.h>
 #include <cstring>
+#include <vector>
 #include "heat_ctx.cuh"
 
 namespace heat {
@@ -24,6 +35,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
     ncclResult_t (*GetVersion)(int *) = nullptr;
 };
@@ -44,6 +56,7 @@ NcclApi *nccl()
             HEAT_SYM(CommInitRank, "ncclCommInitRank");
             HEAT_SYM(CommDestroy, "ncclCommDestroy");
             HEAT_SYM(AllReduce, "ncclAllReduce");
+            HEAT_SYM(AllGather, "ncclAllGather");
             HEAT_SYM(GetErrorString, "ncclGetErrorString");
             HEAT_SYM(GetVersion, "ncclGetVersion");
 #undef HEAT_SYM
@@ -80,7 +93,170 @@ __global__ void apply_kernel(float4 *__restrict__ w, float4 *__restrict__ base, 
     }
 }
 
+// ---- fused exchange over peer memory ------------------------------------------------------------------------
+constexpr int MAX_PEERS = 8;
+struct PeerSync {
+    int rank, world;
+    float4 *w[MAX_PEERS], *base[MAX_PEERS];        // item table / base copy of every rank (peer-mapped; [rank] = local)
+    float4 *w0[MAX_PEERS], *w0b[MAX_PEERS];
+    unsigned long long *flags[MAX_PEERS];          // [2][8] arrival counters of every rank
+    unsigned long long seq;                        // this exchange's number (1, 2, ...)
+    float scale;
+    size_t n4_items, n4_w0;
+    unsigned *grid_sync;                           // [0] release flag of the start barrier, [1] blocks done
+};
+
+__device__ __forceinline__ float4 ld_sys4(const float4 *p)
+{
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_sys4(float4 *p, const float4 &v)
+{
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned *p, unsigned v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// all ranks: flags[q][which][rank] = seq on every rank q, then wait until every rank has written mine
+__device__ __forceinline__ void peer_barrier(const PeerSync &S, int which)
+{
+    if ((int)threadIdx.x < S.world) {
+        const int q = (int)threadIdx.x;
+        __threadfence_system();
+        st_release_sys(S.flags[q] + which * MAX_PEERS + S.rank, S.seq);
+        while (ld_acquire_sys(S.flags[S.rank] + which * MAX_PEERS + q) < S.seq) { }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void peer_reduce_range(const PeerSync &S, float4 *const *w, float4 *const *base, size_t n4)
+{
+    const size_t per = (n4 + S.world - 1) / S.world;
+    const size_t lo = per * S.rank, hi = lo + per < n4 ? lo + per : n4;
+    for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 b = base[S.rank][i];
+        float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < S.world; ++q) {
+            const float4 a = ld_sys4(w[q] + i);
+            d.x += a.x - b.x; d.y += a.y - b.y; d.z += a.z - b.z; d.w += a.w - b.w;
+        }
+        float4 nb;
+        nb.x = fmaf(S.scale, d.x, b.x); nb.y = fmaf(S.scale, d.y, b.y); nb.z = fmaf(S.scale, d.z, b.z); nb.w = fmaf(S.scale, d.w, b.w);
+        for (int q = 0; q < S.world; ++q) { st_sys4(w[q] + i, nb); st_sys4(base[q] + i, nb); }
+    }
+}
+
+__global__ void __launch_bounds__(256) peer_sync_kernel(const PeerSync S)
+{
+    const unsigned seq32 = (unsigned)S.seq;
+    // start barrier: every rank's training kernel has finished (this kernel follows it on the rank's stream)
+    if (blockIdx.x == 0) {
+        peer_barrier(S, 0);
+        if (threadIdx.x == 0) st_release_gpu(S.grid_sync, seq32);
+    } else {
+        if (threadIdx.x == 0) while (ld_acquire_gpu(S.grid_sync) != seq32) { }
+        __syncthreads();
+    }
+    peer_reduce_range(S, S.w, S.base, S.n4_items);
+    peer_reduce_range(S, S.w0, S.w0b, S.n4_w0);
+    // end barrier: my stores have landed in every replica and every peer's stores have landed in mine before any
+    // later kernel of this stream starts; the last block to finish carries it
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x == 0) last = atomicAdd(S.grid_sync + 1, 1u) + 1u == seq32 * gridDim.x;
+    __syncthreads();
+    if (last) peer_barrier(S, 1);
+}
+
+// Map every rank's buffers (CUDA IPC handles all-gathered with NCCL).  Any failure leaves peer_ok false: NCCL path.
+int peer_setup(Ctx *c, NcclApi *api)
+{
+    if (c->world > MAX_PEERS || c->cfg.exchange_mode == 1 || !api->AllGather) return 0;
+    HEAT_CUDA(cudaMalloc(&c->xflags, 2 * MAX_PEERS * sizeof(unsigned long long)));
+    HEAT_CUDA(cudaMemset(c->xflags, 0, 2 * MAX_PEERS * sizeof(unsigned long long)));
+    HEAT_CUDA(cudaMalloc(&c->grid_sync, 2 * sizeof(unsigned)));
+    HEAT_CUDA(cudaMemset(c->grid_sync, 0, 2 * sizeof(unsigned)));
+    struct Export { cudaIpcMemHandle_t h[5]; int ok; int pad[15]; };
+    Export mine{};
+    void *ptrs[5] = {c->item_w, c->item_base, c->w0, c->w0_base, c->xflags};
+    mine.ok = 1;
+    for (int i = 0; i < 5; ++i)
+        if (cudaIpcGetMemHandle(&mine.h[i], ptrs[i]) != cudaSuccess) { mine.ok = 0; cudaGetLastError(); }
+    Export *d_all = nullptr;
+    HEAT_CUDA(cudaMalloc(&d_all, sizeof(Export) * c->world));
+    HEAT_CUDA(cudaMemcpyAsync(d_all + c->rank, &mine, sizeof(Export), cudaMemcpyHostToDevice, c->stream));
+    HEAT_NCCL(api->AllGather(d_all + c->rank, d_all, sizeof(Export), ncclChar, static_cast<ncclComm_t>(c->nccl_comm), c->stream));
+    std::vector<Export> all(c->world);
+    HEAT_CUDA(cudaMemcpyAsync(all.data(), d_all, sizeof(Export) * c->world, cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d_all);
+    bool ok = true;
+    for (int q = 0; q < c->world; ++q) ok = ok && all[q].ok;
+    for (int q = 0; q < c->world && ok; ++q) {
+        void *m[5];
+        if (q == c->rank) {
+            for (int i = 0; i < 5; ++i) m[i] = ptrs[i];
+        } else {
+            for (int i = 0; i < 5 && ok; ++i)
+                if (cudaIpcOpenMemHandle(&m[i], all[q].h[i], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = false; cudaGetLastError(); }
+        }
+        if (!ok) break;
+        c->peer_item_w[q] = static_cast<float *>(m[0]); c->peer_item_base[q] = static_cast<float *>(m[1]);
+        c->peer_w0[q] = static_cast<float *>(m[2]); c->peer_w0_base[q] = static_cast<float *>(m[3]);
+        c->peer_flags[q] = static_cast<unsigned long long *>(m[4]);
+    }
+    // every rank must take the same path: agree on the outcome (a rank that failed to map vetoes)
+    double agree = ok ? 0.0 : 1.0;
+    HEAT_CUDA(cudaMemcpyAsync(c->loss_pair, &agree, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    HEAT_NCCL(api->AllReduce(c->loss_pair, c->loss_pair, 1, ncclDouble, ncclSum, static_cast<ncclComm_t>(c->nccl_comm), c->stream));
+    HEAT_CUDA(cudaMemcpyAsync(&agree, c->loss_pair, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    c->peer_ok = agree == 0.0;
+    return 0;
+}
+
+int peer_sync(Ctx *c)
+{
+    PeerSync S{};
+    S.rank = c->rank; S.world = c->world;
+    for (int q = 0; q < c->world; ++q) {
+        S.w[q] = reinterpret_cast<float4 *>(c->peer_item_w[q]); S.base[q] = reinterpret_cast<float4 *>(c->peer_item_base[q]);
+        S.w0[q] = reinterpret_cast<float4 *>(c->peer_w0[q]); S.w0b[q] = reinterpret_cast<float4 *>(c->peer_w0_base[q]);
+        S.flags[q] = c->peer_flags[q];
+    }
+    const size_t D = c->cfg.emb_dim;
+    S.seq = c->syncs + 1;
+    S.scale = c->cfg.sync_average ? 1.0f / (float)c->world : 1.0f;
+    S.n4_items = c->cfg.num_items * D / 4; S.n4_w0 = D * D / 4;
+    S.grid_sync = c->grid_sync;
+    peer_sync_kernel<<<c->num_sms, 256, 0, c->stream>>>(S);       // one resident block per SM: the spin barriers need co-residency
+    HEAT_CUDA(cudaGetLastError());
+    c->launches += 1;
+    c->syncs += 1;
+    return 0;
+}
+
 }  // namespace
+
+int comm_mode(const Ctx *c) { return (c->world <= 1 || !c->nccl_comm) ? 0 : (c->peer_ok ? 2 : 1); }
 
 int comm_unique_id(uint8_t out[128])
 {
@@ -114,13 +290,14 @@ int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128])
     HEAT_CUDA(cudaMemcpyAsync(c->item_base, c->item_w, ib, cudaMemcpyDeviceToDevice, c->stream));
     HEAT_CUDA(cudaMemcpyAsync(c->w0_base, c->w0, wb, cudaMemcpyDeviceToDevice, c->stream));
     HEAT_CUDA(cudaStreamSynchronize(c->stream));
-    return 0;
+    return peer_setup(c, api);
 }
 
 // Reconcile the replicated item table and W0 across ranks (see the header comment).
 int comm_sync_items(Ctx *c)
 {
     if (c->world <= 1 || !c->nccl_comm) return 0;
+    if (c->peer_ok) return peer_sync(c);
     NcclApi *api = nccl();
     const size_t D = c->cfg.emb_dim, in4 = c->cfg.num_items * D / 4, wn4 = D * D / 4;
     float4 *delta = reinterpret_cast<float4 *>(c->delta);
@@ -192,8 +369,16 @@ void comm_destroy(Ctx *c)
         if (api) api->CommDestroy(static_cast<ncclComm_t>(c->nccl_comm));
         c->nccl_comm = nullptr;
     }
-    cudaFree(c->delta); cudaFree(c->loss_pair);
-    c->delta = nullptr; c->loss_pair = nullptr;
+    if (c->peer_ok) {
+        for (int q = 0; q < c->world; ++q) {
+            if (q == c->rank) continue;
+            cudaIpcCloseMemHandle(c->peer_item_w[q]); cudaIpcCloseMemHandle(c->peer_item_base[q]);
+            cudaIpcCloseMemHandle(c->peer_w0[q]); cudaIpcCloseMemHandle(c->peer_w0_base[q]); cudaIpcCloseMemHandle(c->peer_flags[q]);
+        }
+        c->peer_ok = false;
+    }
+    cudaFree(c->delta); cudaFree(c->loss_pair); cudaFree(c->xflags); cudaFree(c->grid_sync);
+    c->delta = nullptr; c->loss_pair = nullptr; c->xflags = nullptr; c->grid_sync = nullptr;
 }
 
 }  // namespace heat

@@ -496,6 +496,14 @@ int heat_comm_allreduce_f64(heat_ctx *ctx, double *vals, int n)
     HEAT_CUDA(cudaSetDevice(c->device));
     return comm_allreduce_f64(c, vals, n);
 }
+int heat_comm_mode(heat_ctx *ctx, int *mode)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c || !mode) return fail("heat_comm_mode: null argument");
+    *mode = comm_mode(c);
+    return 0;
+}
+
 int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples)
 {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);

@@ -43,6 +43,12 @@ struct Ctx {
     float *item_base = nullptr, *w0_base = nullptr, *delta = nullptr;
     double *loss_pair = nullptr;
     uint64_t sync_interval = 0, syncs = 0;
+    // fused exchange over NVLink peer memory (comm.cu): every rank's tables and flags mapped through CUDA IPC
+    bool peer_ok = false;
+    float *peer_item_w[8] = {}, *peer_item_base[8] = {}, *peer_w0[8] = {}, *peer_w0_base[8] = {};
+    unsigned long long *peer_flags[8] = {};    // [2][8] arrival counters per rank: [0] start barrier, [1] end barrier
+    unsigned long long *xflags = nullptr;      // this rank's flags
+    unsigned *grid_sync = nullptr;             // intra-grid release flag and done counter of peer_sync_kernel
 
     // evaluation scratch (lazily sized)
     void *eval_scratch = nullptr;
@@ -85,6 +91,7 @@ void eval_free(Ctx *c);
 int comm_unique_id(uint8_t out[128]);
 int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128]);
 int comm_sync_items(Ctx *c);
+int comm_mode(const Ctx *c);
 int comm_reduce_loss(Ctx *c, double *loss_sum, double *samples);
 int comm_allreduce_f64(Ctx *c, double *vals, int n);
 int comm_max_u64(Ctx *c, uint64_t *v);

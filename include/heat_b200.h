@@ -71,6 +71,10 @@ typedef struct heat_config {
                                    CTA kernel runs min(#SMs, max(8, num_items/600)) blocks (one sample in flight per
                                    ~600 item rows keeps Recall@20 on the reference's); engines
                                    1 and 2 use one grid over all SMs */
+    uint32_t exchange_mode;     /* multi-GPU item/W0 reconciliation: 0 auto -- ONE kernel per rank that reads every rank's
+                                   replica over NVLink peer memory (CUDA IPC), reduces its slice of the rows and writes
+                                   the result back into every replica (comm.cu); NCCL all-reduce when peer mapping is
+                                   not available; 1 = always NCCL (delta kernel + ncclAllReduce + apply kernel) */
     uint32_t tile_sampler;      /* 1 with neg_sampler 1: hot-tile policy (random_tile_negative_sampler.cpp:22-45, paper
                                    Alg. 1): the samples of one window of refresh_interval samples draw their negatives
                                    from a Philox-defined tile of tile_size item ids (philox.cuh).  0 (default): as the
@@ -193,6 +197,8 @@ int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[1
  * the W0 delta since the last sync; every rank ends with base + sum of deltas. */
 int heat_comm_sync_items(heat_ctx *ctx);
 int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);   /* 0 = once per epoch */
+/* how heat_comm_sync_items exchanges: 0 no communicator, 1 NCCL all-reduce, 2 fused peer-memory kernel */
+int heat_comm_mode(heat_ctx *ctx, int *mode);
 /* replaces: MPI_Allreduce of loss / iteration count (engine.cpp:380-383) for caller-side sums, e.g. the
  * seven metric sums of heat_eval_metrics on user-sharded evaluation: vals[n] (n <= 16) summed over ranks. */
 int heat_comm_allreduce_f64(heat_ctx *ctx, double *vals, int n);
