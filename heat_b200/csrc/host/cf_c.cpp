@@ -50,7 +50,8 @@ PYBIND11_MODULE(cf_c, cf_module)
         .def_readwrite("sync_average", &CFConfig::sync_average)
         .def_readwrite("history_mode", &CFConfig::history_mode)
         .def_readwrite("engine", &CFConfig::engine)
-        .def_readwrite("tile_sampler", &CFConfig::tile_sampler);
+        .def_readwrite("tile_sampler", &CFConfig::tile_sampler)
+        .def_readwrite("exchange_mode", &CFConfig::exchange_mode);
 
     py::module_ datasets = m.def_submodule("datasets", "datasets");
     py::class_<Dataset, std::shared_ptr<Dataset>>(datasets, "Dataset");
