@@ -8,8 +8,13 @@
 // critical path.  Warp roles (every warp is role-uniform):
 //
 //   neg warps   16 slots of D/4 lanes; slot q owns the negative rows k = q, q+16, ... (NPS per slot).
-//               The same 4D threads hold W0 in REGISTERS (D/4 rows of one column each), compute mean.W0 and
-//               apply the batched W0 step every 32 samples from shared-memory rings of (mean, 0.6 g_u).
+//               The same 4D threads apply the batched W0 step every 32 samples from shared-memory rings of
+//               (mean, 0.6 g_u), D/4 rows of one column each, and leave the stepped W0 in shared memory.
+//   gemv warp   D/32 columns of W0 per lane in REGISTERS: f = mean . W0 of the next sample while the other
+//               warps are still storing rows (it used to sit on the neg warps, the last to reach [G1]).  It
+//               runs its own copy of the loop skeleton (same barriers, no row work), so that its D^2/32
+//               registers are not live in the row warps' code; one warp keeps the CTA at 12 warps = 3 per
+//               scheduler (168 registers a thread).
 //   pos warp    the positive row, the loss, the patch of the cached history column sums -> next history mean.
 //   usr warp    the user row, kept in registers across a user's run.
 //   ctl warp    runs ahead on its own loop: one LANE per sample, 32 samples per batch -- click, Philox
@@ -21,7 +26,7 @@
 //        interleaved butterfly; E_k = exp(cos_k/T) and the UNNORMALISED partial user grads, published per slot
 //   [A]  all: esum = 1 + exp(-cos_p/T) * sum_k E_k from 16 shared partials (no cross-slot shuffles);
 //        usr: user grad, aggregator backward, clipped step, next sample's input row     (the critical chain)
-//        pos: clipped step, patched column sums, next history mean -> named barrier 3 -> neg: mean.W0 of the next sample
+//        pos: clipped step, patched column sums, next history mean -> named barrier 3 -> gemv: mean.W0 of the next sample
 //        neg: clipped row steps, stores
 //   Rows come from the prefetch slots; a sample sharing an item row with its predecessor ("late") or starting
 //   a run ("fresh": history gather) loads after an extra barrier, behind the predecessor's stores.
@@ -52,11 +57,12 @@ template <int D, int NPS> struct CtaCfg {
     static_assert(D == 32 || D == 64, "the CTA engine covers emb_dim 32 and 64");
     static constexpr int LPR = D / 4;                       // lanes per row
     static constexpr int NEGT = 16 * LPR;                    // threads of the negative slots (whole warps)
-    static constexpr int POS0 = NEGT, USR0 = POS0 + 32, CTRL0 = USR0 + 32;
+    static constexpr int POS0 = NEGT, USR0 = POS0 + 32, GMV0 = USR0 + 32, CTRL0 = GMV0 + 32;
+    static constexpr int NLD = GMV0;                         // threads that load rows (negative slots, pos, usr)
     static constexpr int NT = CTRL0 + 32;
     static constexpr int NSLOT = 18;
     static constexpr int KMAX = 16 * NPS;
-    static constexpr int IQ = D / 4;                         // W0 rows per neg thread (GEMV and the batched W0 step)
+    static constexpr int IQ = D / 4;                         // W0 rows per neg thread (the batched W0 step)
     static constexpr int MRING = 64, GRING = 32;             // history means of the last 64 samples, 0.6*g_u of the last 32
     // shared memory, in floats
     static constexpr int OFF_MEAN = 0;                       // [MRING][D]
@@ -68,13 +74,14 @@ template <int D, int NPS> struct CtaCfg {
     static constexpr int OFF_PART = OFF_PW + D;              // [16][D] unnormalised user-grad partial sums of the negative slots
     static constexpr int OFF_HPART = OFF_PART + 16 * D;      // [NSLOT][D] history-gather partial sums
     static constexpr int OFF_SC = OFF_HPART + NSLOT * D;     // sE[16], sB[16], pp, up, Ep
-    static constexpr int OFF_RING = OFF_SC + 40;             // 3 x CtaBatch
-    static constexpr int OFF_STAGE = OFF_RING + 3 * (int)(sizeof(CtaBatch<NPS>) / 4);   // [2*NPS][CTRL0] float4: prefetched rows
-    static constexpr int FLOATS = OFF_STAGE + 2 * NPS * CTRL0 * 4 + 8;
+    static constexpr int OFF_W0S = OFF_SC + 40;              // [D][D] W0 as of this CTA's last step (neg warps -> gemv warp)
+    static constexpr int OFF_RING = OFF_W0S + D * D;         // 3 x CtaBatch
+    static constexpr int OFF_STAGE = OFF_RING + 3 * (int)(sizeof(CtaBatch<NPS>) / 4);   // [2*NPS][NLD] float4: prefetched rows
+    static constexpr int FLOATS = OFF_STAGE + 2 * NPS * NLD * 4 + 8;
 };
 
 // named barriers: 1 = the row warps, 2 = row warps + control warp (once per batch),
-// 3 = pos warp (arrives: the next history mean is published) + neg warps (wait for it)
+// 3 = pos warp (arrives: the next history mean is published) + gemv warp (waits for it)
 template <int N> __device__ __forceinline__ void row_bar() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
 template <int N> __device__ __forceinline__ void batch_bar() { asm volatile("bar.sync 2, %0;" ::"n"(N) : "memory"); }
 template <int N> __device__ __forceinline__ void mean_arrive() { asm volatile("bar.arrive 3, %0;" ::"n"(N) : "memory"); }
@@ -236,10 +243,11 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW;
     float *part = smem + C::OFF_PART, *hpart = smem + C::OFF_HPART;
     float *sE = smem + C::OFF_SC, *sB = sE + 16, *sc3 = sB + 16;      // sc3: pp, up, Ep
+    float *w0s = smem + C::OFF_W0S;
     CtaBatch<NPS> *ring = reinterpret_cast<CtaBatch<NPS> *>(smem + C::OFF_RING);
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const int role = tid < C::NEGT ? 0 : tid < C::USR0 ? 1 : tid < C::CTRL0 ? 2 : 3;   // warp-uniform
+    const int role = tid < C::NEGT ? 0 : tid < C::USR0 ? 1 : tid < C::GMV0 ? 2 : tid < C::CTRL0 ? 4 : 3;   // warp-uniform
     const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
     const bool no_cache = P.no_cache != 0;
 
@@ -267,40 +275,94 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         }
     }
 
+    // ======== gemv warp: the row warps' loop skeleton (same barriers, same block-uniform conditions), no row work ========
+    if (role == 4) {
+        constexpr int CPL = D / 32;                          // adjacent columns of W0 per lane
+        float wcol[D][CPL];
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) wcol[k][c] = __ldcg(P.w0 + k * D + CPL * lane + c);
+        // f = mean . W0 (behavior_aggregators.cpp:118): per column four row quarters of four interleaved chains each
+        auto gemv = [&](const float *mean_) {
+            float fr[4][CPL];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float f[4][CPL];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int c = 0; c < CPL; ++c) f[j][c] = 0.f;
+#pragma unroll
+                for (int i4 = 0; i4 < IQ; i4 += 4) {
+                    const float4 m4 = *reinterpret_cast<const float4 *>(mean_ + q * IQ + i4);
+                    const float mj[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+#pragma unroll
+                        for (int c = 0; c < CPL; ++c) f[j][c] = fmaf(mj[j], wcol[q * IQ + i4 + j][c], f[j][c]);
+                }
+#pragma unroll
+                for (int c = 0; c < CPL; ++c) fr[q][c] = (f[0][c] + f[1][c]) + (f[2][c] + f[3][c]);
+            }
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) f_s[CPL * lane + c] = (fr[0][c] + fr[1][c]) + (fr[2][c] + fr[3][c]);
+        };
+        bool have_f = false;
+        unsigned it = 0;
+        batch_bar<NT>();                                     // #1
+        for (int rbuf = 0;; rbuf = rbuf == 2 ? 0 : rbuf + 1) {
+            const CtaBatch<NPS> *Bt = &ring[rbuf], *Bn = &ring[rbuf == 2 ? 0 : rbuf + 1];
+            const int cnt = Bt->cnt;
+            if (cnt == 0) break;
+            for (int j = 0; j < cnt; ++j) {
+                const CtaMeta<NPS> *mn = (j + 1 < cnt) ? &Bt->meta[j + 1] : (Bn->cnt > 0 ? &Bn->meta[0] : nullptr);
+                const int fl = Bt->meta[j].flags, nfl = mn ? mn->flags : 0;
+                if (fl & CTA_LATE) row_bar<NROW>();
+                if (fl & CTA_FRESH) { row_bar<NROW>(); row_bar<NROW>(); row_bar<NROW>(); }   // the history gather
+                if (it > 0 && (it & 31) == 0) {               // a W0 step: the neg warps leave the stepped W0 in w0s
+                    row_bar<NROW>();
+                    row_bar<NROW>();
+#pragma unroll
+                    for (int k = 0; k < D; ++k) {
+                        if constexpr (CPL == 2) {
+                            const float2 w2 = *reinterpret_cast<const float2 *>(w0s + k * D + 2 * lane);
+                            wcol[k][0] = w2.x; wcol[k][1] = w2.y;
+                        } else {
+                            wcol[k][0] = w0s[k * D + lane];
+                        }
+                    }
+                }
+                if (!have_f) gemv(mean_ring + (it & (MRING - 1)) * D);
+                row_bar<NROW>();                              // [G1]
+                row_bar<NROW>();                              // [A]: f_s has been consumed
+                have_f = mn != nullptr && !(nfl & CTA_FRESH) && ((it + 1) & 31) != 0;
+                mean_wait<64>();                              // the pos warp has published the next history mean
+                if (have_f) gemv(mean_ring + ((it + 1) & (MRING - 1)) * D);   // off everyone's critical path
+                if (fl & CTA_DUP)
+                    for (int k = 0; k < P.K; ++k) row_bar<NROW>();
+                it += 1;
+            }
+            batch_bar<NT>();
+        }
+        row_bar<NROW>();                                     // the leftover W0 step
+        return;
+    }
+
     // ======== row warps ========
     const int sl = tid % LPR;                                // lane within the row slot (the pos / usr warps mirror their slot)
     const int slot = role == 0 ? tid / LPR : 15 + role;      // 0..15 negatives, 16 positive, 17 user
     float *stage = smem + C::OFF_STAGE + 4 * tid;            // this thread's prefetch slots: [2n] weight, [2n+1] grad slice
-    constexpr int STG = NROW * 4;                            // floats between two slots
+    constexpr int STG = C::NLD * 4;                          // floats between two slots
 
     const float gamma = 0.4f, omg = 1.0f - gamma;
     const float score_mul = (float)(1.0 / 0.07);
     const int K = P.K;
 
-    // neg threads: slice of W0 (rows rb*IQ .. +IQ of column col) in registers; 4 lanes share a column
+    // neg threads: rows rb*IQ .. +IQ of column col of W0 in the batched step; 4 lanes share a column
     const int col = tid >> 2, rb = tid & 3;
-    float wreg[IQ];
-    if (role == 0) {
-#pragma unroll
-        for (int i = 0; i < IQ; ++i) wreg[i] = __ldcg(P.w0 + (rb * IQ + i) * D + col);
-    }
-    // f = mean . W0 (behavior_aggregators.cpp:118): IQ FMAs per thread, two shuffles
-    auto gemv = [&](const float *mean_) {
-        const float *pm = mean_ + rb * IQ;
-        float f0 = 0.f, f1 = 0.f, f2 = 0.f, f3 = 0.f;
-#pragma unroll
-        for (int i4 = 0; i4 < IQ; i4 += 4) {
-            const float4 m4 = *reinterpret_cast<const float4 *>(pm + i4);
-            f0 = fmaf(m4.x, wreg[i4], f0); f1 = fmaf(m4.y, wreg[i4 + 1], f1);
-            f2 = fmaf(m4.z, wreg[i4 + 2], f2); f3 = fmaf(m4.w, wreg[i4 + 3], f3);
-        }
-        float f = (f0 + f1) + (f2 + f3);
-        f += __shfl_xor_sync(FULL, f, 1);
-        f += __shfl_xor_sync(FULL, f, 2);
-        if (rb == 0) f_s[col] = f;
-    };
     // neg threads: the W0 step of the last `ns` samples (behavior_aggregators.cpp:131-146) as one batched
-    // rank-ns update from the rings: W0 -= lr0 * (sum_s mean_s^T (0.6 g_s)) / 32; the thread's slice is refreshed
+    // rank-ns update from the rings: W0 -= lr0 * (sum_s mean_s^T (0.6 g_s)) / 32; the stepped slice goes to w0s
     auto w0_step = [&](unsigned upto, int ns) {
         float acc[IQ];
 #pragma unroll
@@ -320,7 +382,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         for (int i = 0; i < IQ; ++i) {
             const float delta = -(P.lr_w0 * (acc[i] / 32.0f));
             const float old = atomicAdd(P.w0 + (rb * IQ + i) * D + col, delta);   // returns the value before: picks up other CTAs' steps
-            wreg[i] = old + delta;
+            w0s[(rb * IQ + i) * D + col] = old + delta;
         }
     };
 
@@ -328,7 +390,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     int keep_u = -1, pf_u = -1;                              // usr: user of u_keep; user whose row is in the prefetch slot
     bool urow_done = false;                                  // usr: urow_s already holds this sample's user row
     bool have_pf = false;                                    // the prefetch slots hold this sample's item rows
-    bool have_f = false;                                     // f_s already holds this sample's mean . W0
     int nidn[NPS];
     unsigned it = 0;                                         // samples processed by this CTA
     double loss_acc = 0.0;
@@ -383,7 +444,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     rw = ldcg4(P.item_w + (size_t)p * D + 4 * sl);
                     rg = ldcg4(P.item_g + (size_t)p * D + 4 * sl);
                 }
-            } else {
+            } else if (role == 2) {
                 if (u == keep_u) {                             // the run continues: the row is in registers
                     rw = u_keep; rg = gu_keep;
                 } else if (pf_u == u) {
@@ -426,8 +487,9 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             if (it > 0 && (it & 31) == 0) {
                 row_bar<NROW>();                              // the rings hold the last 32 samples
                 if (role == 0) w0_step(it, 32);
+                row_bar<NROW>();                              // the stepped W0 is in w0s
             }
-            if (role == 0 && !have_f) gemv(mean);
+            // (gemv warp: f = mean . W0 now, unless it was computed during the previous sample)
             HEAT_PT(2);
             row_bar<NROW>();                                                          // [G1]
             // ---- prefetch of the next sample's rows (ordered after every store of the previous sample by [G1];
@@ -499,7 +561,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 const float cos_p = upd * (rinv_u * rsqrt_eps(pp));
                 if (sl == 0) { sc3[0] = pp; sc3[1] = upd; sc3[2] = expf(-(cos_p * score_mul)); }
                 *reinterpret_cast<float4 *>(pw_s + 4 * sl) = rw;
-            } else {
+            } else if (role == 2) {
                 float r[1] = {dot4(ua, ua)};
                 group_sum_n<LPR, 1>(r);
                 uu = r[0];
@@ -520,7 +582,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             const float Ep = sc3[2];
             const float esum = fmaf(Ep, SE, 1.0f);
             const float cE = (Ep * score_mul) / esum;
-            have_f = mn != nullptr && !(nfl & CTA_FRESH) && ((it + 1) & 31) != 0;   // next mean.W0 can be computed now
             float c1[NPS], c2[NPS];
             float4 gp = f4zero();
             HEAT_PT(6);
@@ -569,7 +630,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 *reinterpret_cast<float4 *>(accs + 4 * sl) = a4;
                 *reinterpret_cast<float4 *>(mean_next + 4 * sl) = m->rH * a4;
                 __syncwarp();
-                mean_arrive<C::NEGT + 32>();
+                mean_arrive<64>();
             } else {
                 // ---- negative rows: lg*gn_n = c1*u + c2*N[k] (:139-143), clipped step, write-back (:127-150; sgd.cpp:14-26)
 #pragma unroll
@@ -593,9 +654,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     }
                 }
                 HEAT_PT(7);
-                mean_wait<C::NEGT + 32>();                     // the pos warp has published the next history mean
-                HEAT_PT(8);
-                if (have_f) gemv(mean_next);                   // mean.W0 of the next sample, off its critical path
             }
             HEAT_PT(4);
             if (dup) {
