@@ -11,11 +11,11 @@
 //               The same 4D threads apply the batched W0 step every 32 samples from shared-memory rings of
 //               (mean, 0.6 g_u), D/4 rows of one column each, and leave the stepped W0 in shared memory.
 //   gemv warp   D/32 columns of W0 per lane in REGISTERS: f = mean . W0 of the next sample while the other
-//               warps are still storing rows (it used to sit on the neg warps, the last to reach [G1]).  It
-//               runs its own copy of the loop skeleton (same barriers, no row work), so that its D^2/32
-//               registers are not live in the row warps' code; one warp keeps the CTA at 12 warps = 3 per
-//               scheduler (168 registers a thread).
-//   pos warp    the positive row, the loss, the patch of the cached history column sums -> next history mean.
+//               warps are still storing rows (it used to sit on the neg warps, the last to reach [G1]); also
+//               the loss (log esum and its running sums).  It runs its own copy of the loop skeleton (same
+//               barriers, no row work), so that its D^2/32 registers are not live in the row warps' code;
+//               one warp keeps the CTA at 12 warps = 3 per scheduler (168 registers a thread).
+//   pos warp    the positive row, the patch of the cached history column sums -> next history mean.
 //   usr warp    the user row, kept in registers across a user's run.
 //   ctl warp    runs ahead on its own loop: one LANE per sample, 32 samples per batch -- click, Philox
 //               negatives, duplicate / conflict detection, history membership -- into a ring of three
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     float *mean_ring = smem + C::OFF_MEAN, *gu06_ring = smem + C::OFF_GU06, *accs = smem + C::OFF_ACC, *f_s = smem + C::OFF_F;
     float *urow_s = smem + C::OFF_UROW, *pw_s = smem + C::OFF_PW;
     float *part = smem + C::OFF_PART, *hpart = smem + C::OFF_HPART;
-    float *sE = smem + C::OFF_SC, *sB = sE + 16, *sc3 = sB + 16;      // sc3: pp, up, Ep
+    float *sE = smem + C::OFF_SC, *sB = sE + 16, *sc3 = sB + 16;      // sc3: pp, up, Ep, 1/|p|
     float *w0s = smem + C::OFF_W0S;
     CtaBatch<NPS> *ring = reinterpret_cast<CtaBatch<NPS> *>(smem + C::OFF_RING);
 
@@ -310,6 +310,8 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         };
         bool have_f = false;
         unsigned it = 0;
+        double loss_acc = 0.0;
+        float loss_f = 0.f;
         batch_bar<NT>();                                     // #1
         for (int rbuf = 0;; rbuf = rbuf == 2 ? 0 : rbuf + 1) {
             const CtaBatch<NPS> *Bt = &ring[rbuf], *Bn = &ring[rbuf == 2 ? 0 : rbuf + 1];
@@ -337,6 +339,19 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 row_bar<NROW>();                              // [G1]
                 row_bar<NROW>();                              // [A]: f_s has been consumed
                 have_f = mn != nullptr && !(nfl & CTA_FRESH) && ((it + 1) & 31) != 0;
+                {
+                    // loss = log(esum) (matrix_factorization.cpp:108), esum exactly as the row warps form it below
+                    const float4 e0 = *reinterpret_cast<const float4 *>(sE), e1 = *reinterpret_cast<const float4 *>(sE + 4);
+                    const float4 e2 = *reinterpret_cast<const float4 *>(sE + 8), e3 = *reinterpret_cast<const float4 *>(sE + 12);
+                    const float4 e = (e0 + e1) + (e2 + e3);
+                    const float esum = fmaf(sc3[2], (e.x + e.y) + (e.z + e.w), 1.0f);
+                    if (lane == 0) {
+                        const float loss = logf(esum);
+                        loss_f += loss;
+                        if ((it & 31) == 31) { loss_acc += (double)loss_f; loss_f = 0.f; }
+                        if (P.loss_out) P.loss_out[Bt->meta[j].s - P.begin] = loss;
+                    }
+                }
                 mean_wait<64>();                              // the pos warp has published the next history mean
                 if (have_f) gemv(mean_ring + ((it + 1) & (MRING - 1)) * D);   // off everyone's critical path
                 if (fl & CTA_DUP)
@@ -346,6 +361,10 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             batch_bar<NT>();
         }
         row_bar<NROW>();                                     // the leftover W0 step
+        if (lane == 0) {
+            loss_acc += (double)loss_f;
+            if (loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
+        }
         return;
     }
 
@@ -392,8 +411,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     bool have_pf = false;                                    // the prefetch slots hold this sample's item rows
     int nidn[NPS];
     unsigned it = 0;                                         // samples processed by this CTA
-    double loss_acc = 0.0;
-    float loss_f = 0.f;
 #ifdef HEAT_CTA_PROFILE
     const bool prof_on = blockIdx.x == 0 && lane == 0;
     long long prof_abs[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -558,8 +575,9 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 group_sum_n<LPR, 3>(r);
                 uu = r[0]; pp = r[1]; upd = r[2];
                 rinv_u = rsqrt_eps(uu);
-                const float cos_p = upd * (rinv_u * rsqrt_eps(pp));
-                if (sl == 0) { sc3[0] = pp; sc3[1] = upd; sc3[2] = expf(-(cos_p * score_mul)); }
+                const float rinv_p = rsqrt_eps(pp);
+                const float cos_p = upd * (rinv_u * rinv_p);
+                if (sl == 0) { sc3[0] = pp; sc3[1] = upd; sc3[2] = expf(-(cos_p * score_mul)); sc3[3] = rinv_p; }
                 *reinterpret_cast<float4 *>(pw_s + 4 * sl) = rw;
             } else if (role == 2) {
                 float r[1] = {dot4(ua, ua)};
@@ -602,7 +620,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 const float SB = (b.x + b.y) + (b.z + b.w);
                 pp = sc3[0]; upd = sc3[1];
                 const float4 pw = *reinterpret_cast<const float4 *>(pw_s + 4 * sl);
-                const float q3 = (cE * SE) * ((rinv_u * rinv_u) * (rinv_u * rsqrt_eps(pp)));   // lgsum / (|u|^3 |p|)
+                const float q3 = (cE * SE) * ((rinv_u * rinv_u) * (rinv_u * sc3[3]));   // lgsum / (|u|^3 |p|)
                 // sum_k lg_k*gu_n_k - lgsum*gu_p;  gu_n = (uu*n - un*u)/(|u|^3|n|),  gu_p = (uu*p - up*u)/(|u|^3|p|)
                 float4 gu = rg;
                 fma4(gu, cE, (g0 + g1) + (g2 + g3));
@@ -679,17 +697,11 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 }
             }
             if (role == 1) {
-                // positive row write-back (:173-174); loss (:108)
+                // positive row write-back (:173-174); the loss is the gemv warp's
                 float4 wp = rw;
                 fma4(wp, -P.lr, gp);
                 stcg4(P.item_w + (size_t)p * D + 4 * sl, wp);
                 stcg4(P.item_g + (size_t)p * D + 4 * sl, gp);
-                if (lane == 0) {
-                    const float loss = logf(esum);
-                    loss_f += loss;
-                    if ((it & 31) == 31) { loss_acc += (double)loss_f; loss_f = 0.f; }
-                    if (P.loss_out) P.loss_out[m->s - P.begin] = loss;
-                }
             }
             HEAT_PT(5);
 #ifdef HEAT_CTA_PROFILE
@@ -707,10 +719,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     {
         const int left = (it & 31) == 0 ? (it > 0 ? 32 : 0) : (P.drop_w0_tail ? 0 : (int)(it & 31));
         if (left > 0 && role == 0) w0_step(it, left);
-    }
-    if (role == 1 && lane == 0) {
-        loss_acc += (double)loss_f;
-        if (loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
     }
 }
 
