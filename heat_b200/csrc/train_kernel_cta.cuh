@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             // ---- the rows of this sample: prefetched during the previous sample, or loaded now (first sample,
             //      or a sample sharing an item row with its predecessor: after that one's stores)
             if (fl & CTA_LATE) row_bar<NROW>();
-            int nid[NPS];
+            int nid[NPS], pn = 0;
             float4 nw[NPS], gn[NPS];
             float4 rw = f4zero(), rg = f4zero();              // positive / user weight and grad slices
             if (role == 0) {
@@ -453,7 +453,12 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                         gn[n] = k < K ? ldcg4(P.item_g + (size_t)nid[n] * D + 4 * sl) : f4zero();
                     }
                 }
+                if (pf) {                                      // ids of the rows prefetched after [G1]: read them off its path
+#pragma unroll
+                    for (int n = 0; n < NPS; ++n) nidn[n] = slot + 16 * n < K ? mn->negid[slot + 16 * n] : 0;
+                }
             } else if (role == 1) {
+                if (pf) pn = mn->p;
                 if (have_pf) {
                     cp_async_wait0();
                     rw = *reinterpret_cast<const float4 *>(stage); rg = *reinterpret_cast<const float4 *>(stage + STG);
@@ -516,7 +521,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
 #pragma unroll
                     for (int n = 0; n < NPS; ++n) {
                         const int k = slot + 16 * n;
-                        nidn[n] = k < K ? mn->negid[k] : 0;
                         if (k < K) {
                             cp_async16(stage + (2 * n) * STG, P.item_w + (size_t)nidn[n] * D + 4 * sl);
                             cp_async16(stage + (2 * n + 1) * STG, P.item_g + (size_t)nidn[n] * D + 4 * sl);
@@ -524,8 +528,8 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     }
                     cp_async_commit();
                 } else if (role == 1) {
-                    cp_async16(stage, P.item_w + (size_t)mn->p * D + 4 * sl);
-                    cp_async16(stage + STG, P.item_g + (size_t)mn->p * D + 4 * sl);
+                    cp_async16(stage, P.item_w + (size_t)pn * D + 4 * sl);
+                    cp_async16(stage + STG, P.item_g + (size_t)pn * D + 4 * sl);
                     cp_async_commit();
                 }
             }
