@@ -183,7 +183,7 @@ def run_reference_arm(args, rank, world):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthr, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "loss": loss}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 def workload_config(args, d, world):
@@ -385,7 +385,10 @@ def run_gpu_arm(args, rank, world, local_rank):
     if not args.no_cpu_baseline:
         d0, t0_ = (d, init)
         line["cpu_baseline"] = cpu_baseline(d0, t0_, args.cpu_seconds)
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
+
+
+_JSON_OUT = sys.stdout
 
 
 def main():
@@ -408,6 +411,12 @@ def main():
     ap.add_argument("--ref-step-seconds", type=float, default=4.0)
     ap.add_argument("--ncu-traffic", type=float, default=None, help="dram bytes per launch from profiles/ (ncu --set full)")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: the plugin prints the reference's progress lines with std::cout
+    # (cf_c.modules.test.test_out), so fd 1 points at stderr while the arms run and the line goes to the saved fd
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
