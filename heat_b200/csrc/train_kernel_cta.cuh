@@ -409,7 +409,15 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
     int keep_u = -1, pf_u = -1;                              // usr: user of u_keep; user whose row is in the prefetch slot
     bool urow_done = false;                                  // usr: urow_s already holds this sample's user row
     bool have_pf = false;                                    // the prefetch slots hold this sample's item rows
-    int nidn[NPS];
+    int nidn[NPS];                                           // rows this thread prefetches for the next sample
+    // the prefetch after [G1] is the same two LDGSTS per row for every role: only table and row id differ
+    const float *pf_w = (role == 2 ? P.user_w : P.item_w) + 4 * sl, *pf_g = (role == 2 ? P.user_g : P.item_g) + 4 * sl;
+    unsigned pf_rows = 1u;                                   // bit n: prefetch slot n is in use
+    if (role == 0) {
+        pf_rows = 0u;
+#pragma unroll
+        for (int n = 0; n < NPS; ++n) pf_rows |= (slot + 16 * n < K ? 1u : 0u) << n;
+    }
     unsigned it = 0;                                         // samples processed by this CTA
 #ifdef HEAT_CTA_PROFILE
     const bool prof_on = blockIdx.x == 0 && lane == 0;
@@ -423,11 +431,13 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
         if (cnt == 0) break;
         for (int j = 0; j < cnt; ++j) {
             const CtaMeta<NPS> *m = &Bt->meta[j];
-            const CtaMeta<NPS> *mn = (j + 1 < cnt) ? &Bt->meta[j + 1] : (Bn->cnt > 0 ? &Bn->meta[0] : nullptr);
+            // the next sample's record: always an address inside the ring, valid only if has_next (no 64-bit selects)
+            const bool has_next = j + 1 < cnt || Bn->cnt > 0;
+            const CtaMeta<NPS> *mn = (j + 1 < cnt) ? m + 1 : &Bn->meta[0];
             const int u = m->u, p = m->p, H = m->H, fl = m->flags;
             const bool fresh = (fl & CTA_FRESH) != 0, dup = (fl & CTA_DUP) != 0;
-            const int nfl = mn ? mn->flags : 0, nu = mn ? mn->u : -1;
-            const bool pf = mn != nullptr && !(nfl & CTA_LATE);                  // block-uniform
+            const int nfl = has_next ? mn->flags : 0, nu = has_next ? mn->u : -1;
+            const bool pf = has_next && !(nfl & CTA_LATE);                       // block-uniform
             float *mean = mean_ring + (it & (MRING - 1)) * D;
             float *mean_next = mean_ring + ((it + 1) & (MRING - 1)) * D;
             HEAT_PT(0);
@@ -435,7 +445,8 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             // ---- the rows of this sample: prefetched during the previous sample, or loaded now (first sample,
             //      or a sample sharing an item row with its predecessor: after that one's stores)
             if (fl & CTA_LATE) row_bar<NROW>();
-            int nid[NPS], pn = 0;
+            int nid[NPS];
+            bool pf_me = pf;                                   // this warp prefetches rows of the next sample (warp-uniform)
             float4 nw[NPS], gn[NPS];
             float4 rw = f4zero(), rg = f4zero();              // positive / user weight and grad slices
             if (role == 0) {
@@ -458,7 +469,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     for (int n = 0; n < NPS; ++n) nidn[n] = slot + 16 * n < K ? mn->negid[slot + 16 * n] : 0;
                 }
             } else if (role == 1) {
-                if (pf) pn = mn->p;
+                if (pf) nidn[0] = mn->p;
                 if (have_pf) {
                     cp_async_wait0();
                     rw = *reinterpret_cast<const float4 *>(stage); rg = *reinterpret_cast<const float4 *>(stage + STG);
@@ -477,6 +488,9 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                     rg = ldcg4(P.user_g + (size_t)u * D + 4 * sl);
                 }
                 if (!urow_done) *reinterpret_cast<float4 *>(urow_s + 4 * sl) = rw;
+                pf_me = pf && nu != u;                         // the next sample starts another user's run
+                pf_u = pf_me ? nu : -1;
+                nidn[0] = nu;
             }
             HEAT_PT(1);
             // ---- first sample of a run: gather the history rows (behavior_aggregators.cpp:96-105)
@@ -516,31 +530,15 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
             row_bar<NROW>();                                                          // [G1]
             // ---- prefetch of the next sample's rows (ordered after every store of the previous sample by [G1];
             //      a row shared with THIS sample makes the next one "late" instead)
-            if (pf) {
-                if (role == 0) {
+            if (pf_me) {
 #pragma unroll
-                    for (int n = 0; n < NPS; ++n) {
-                        const int k = slot + 16 * n;
-                        if (k < K) {
-                            cp_async16(stage + (2 * n) * STG, P.item_w + (size_t)nidn[n] * D + 4 * sl);
-                            cp_async16(stage + (2 * n + 1) * STG, P.item_g + (size_t)nidn[n] * D + 4 * sl);
-                        }
+                for (int n = 0; n < NPS; ++n) {
+                    if (pf_rows >> n & 1u) {
+                        cp_async16(stage + (2 * n) * STG, pf_w + (size_t)nidn[n] * D);
+                        cp_async16(stage + (2 * n + 1) * STG, pf_g + (size_t)nidn[n] * D);
                     }
-                    cp_async_commit();
-                } else if (role == 1) {
-                    cp_async16(stage, P.item_w + (size_t)pn * D + 4 * sl);
-                    cp_async16(stage + STG, P.item_g + (size_t)pn * D + 4 * sl);
-                    cp_async_commit();
                 }
-            }
-            if (role == 2) {
-                pf_u = -1;
-                if (pf && nu != u) {                           // the next sample starts another user's run
-                    pf_u = nu;
-                    cp_async16(stage, P.user_w + (size_t)nu * D + 4 * sl);
-                    cp_async16(stage + STG, P.user_g + (size_t)nu * D + 4 * sl);
-                    cp_async_commit();
-                }
+                cp_async_commit();
             }
             have_pf = pf;
             HEAT_PT(9);
