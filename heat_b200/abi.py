@@ -30,6 +30,7 @@ SYMBOLS = [
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
     "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw", "heat_last_engine", "heat_comm_mode",
+    "heat_train_range_noalloc",
 ]
 
 
@@ -46,6 +47,9 @@ class HeatConfig(C.Structure):
         ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("engine", C.c_uint32), ("max_blocks", C.c_uint32),
         ("exchange_mode", C.c_uint32), ("tile_sampler", C.c_uint32),
     ]
+
+
+NOALLOC_MAX_SAMPLES = 1 << 20      # HEAT_NOALLOC_MAX_SAMPLES
 
 
 class HeatError(RuntimeError):
@@ -70,6 +74,7 @@ def lib():
         L.heat_sync_to_host.argtypes = [C.c_void_p]
         L.heat_train_epoch.argtypes = [C.c_void_p, _f64p]
         L.heat_train_range.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _f64p, _f32p]
+        L.heat_train_range_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, _f64p, _f32p]
         L.heat_zero_grad.argtypes = [C.c_void_p]
         L.heat_get_grads.argtypes = [C.c_void_p, _f32p, _f32p]
         L.heat_clickfile_open.argtypes = [C.c_char_p, C.c_char, C.POINTER(C.c_void_p), _u64p, _u64p]
@@ -231,6 +236,13 @@ class Context:
         loss = C.c_double()
         out = np.empty(end - begin, np.float32) if per_sample else None
         _ck(lib().heat_train_range(self._h, begin, end, C.byref(loss), _ptr(out, _f32p)))
+        return (loss.value, out) if per_sample else loss.value
+
+    def train_range_noalloc(self, begin, end, per_sample=False):
+        """heat_train_range without any device allocation (static scratch, <= NOALLOC_MAX_SAMPLES samples per call)."""
+        loss = C.c_double()
+        out = np.empty(end - begin, np.float32) if per_sample else None
+        _ck(lib().heat_train_range_noalloc(self._h, begin, end, C.byref(loss), _ptr(out, _f32p)))
         return (loss.value, out) if per_sample else loss.value
 
     def zero_grad(self):

@@ -191,4 +191,106 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     return rc;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// heat_train_range_noalloc -- heat_train_range for callers that may not allocate (include/heat_b200.h).  Everything the
+// training kernels need beyond the caller's tables lives in ONE file-scope device array: the chunk counter, the fp64
+// loss sum and the per-sample loss staging.  Every GPU that loads the library holds these HEAT_NOALLOC_MAX_SAMPLES*4+256
+// bytes until exit; every call (of every context on that device) shares them, so calls that overlap on the GPU race.
+namespace {
+
+constexpr size_t NOALLOC_HEADER = 256;      // [0,8) chunk counter, [8,16) loss sum, rest padding: the losses start 256-aligned
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_HEADER + (size_t)HEAT_NOALLOC_MAX_SAMPLES * sizeof(float)];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned char *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};     // device address of the array on device d (0 = not set up yet)
+
+// Host code must not use `g_noalloc_scratch` as a pointer: the name is a host-side stand-in.  The device address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+int noalloc_scratch(int device, unsigned char **out)
+{
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail("heat_train_range_noalloc: device index out of range");
+    if (!g_noalloc_ptr[device]) {
+        int cur = -1;
+        HEAT_CUDA(cudaGetDevice(&cur));
+        if (cur != device) return fail("heat_train_range_noalloc: the context's device is not current");
+        void *p = nullptr;
+        HEAT_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return fail("heat_train_range_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return 0;
+}
+
+}  // namespace
+
+int launch_train_noalloc(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host)
+{
+    if (!c->clicks) return fail("heat_set_dataset has not been called");
+    if (!c->user_w) return fail("heat_bind_tables has not been called");
+    if (end > c->n_samples || begin > end) return fail("sample range out of bounds");
+    if (end - begin > (uint64_t)HEAT_NOALLOC_MAX_SAMPLES)
+        return fail("heat_train_range_noalloc: " + std::to_string(end - begin) + " samples exceed HEAT_NOALLOC_MAX_SAMPLES (" +
+                    std::to_string((uint64_t)HEAT_NOALLOC_MAX_SAMPLES) + "), the size of the library's static scratch; split the range");
+    if (c->max_his > 128) return fail("max_his > 128 is not supported by the training kernel");
+    if (loss_sum_host) *loss_sum_host = 0.0;
+    if (begin == end) { c->last_kernel_ms = 0.f; return 0; }
+
+    unsigned char *scratch = nullptr;
+    if (int rc = noalloc_scratch(c->device, &scratch)) return rc;
+    unsigned long long *counter = reinterpret_cast<unsigned long long *>(scratch);
+    double *loss_sum = reinterpret_cast<double *>(scratch + 8);
+    float *loss_out = loss_per_sample_host ? reinterpret_cast<float *>(scratch + NOALLOC_HEADER) : nullptr;
+    // the array keeps the previous call's contents: the counter and the sum must start at zero (the loss slots are all
+    // written by the kernel before they are read back)
+    HEAT_CUDA(cudaMemsetAsync(scratch, 0, 16, c->stream));
+
+    TrainParams P{};
+    P.clicks = c->clicks; P.his = c->his; P.masks = c->masks;
+    P.user_w = c->user_w; P.item_w = c->item_w; P.user_g = c->user_g; P.item_g = c->item_g; P.w0 = c->w0;
+    P.chunk_counter = counter; P.loss_sum = loss_sum; P.loss_out = loss_out;
+    P.begin = (long long)begin; P.end = (long long)end;
+    P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed;
+    set_sampler(c, P);
+    P.epoch = (unsigned)c->epoch;
+    P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
+    P.chunk = (int)c->cfg.chunk;
+    P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
+    P.upd = (int)c->cfg.update_mode;
+    P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
+    P.no_cache = c->cfg.history_mode == 1;
+
+    // same engine choice as launch_train
+    int rc = -1;
+    c->last_engine = 0;
+    const int auto_w = c->cfg.engine == 0 ? auto_warp_engine(c, (int)c->cfg.emb_dim, P.K) : 0;
+    if (auto_w) { rc = dispatch(c, P, false, auto_w); c->last_engine = 1; }
+    else if (c->cfg.engine != 1 && c->cfg.engine != 3) { rc = dispatch_cta(c, P, c->cfg.deterministic != 0); c->last_engine = 2; }
+    if (rc == -1 && c->cfg.engine == 2) rc = fail("engine 2 (CTA per sample) does not cover this (emb_dim, num_negs)");
+    if (rc == -1) {
+        const bool det = c->cfg.deterministic != 0;
+        if (c->cfg.engine == 3 || (c->cfg.engine == 0 && !warp_covers((int)c->cfg.emb_dim, P.K))) { rc = dispatch_bigk(c, P, det); c->last_engine = 3; }
+        else { rc = dispatch(c, P, det); c->last_engine = 1; }
+    }
+    if (rc) return rc;
+    double loss = 0.0;
+    cudaError_t e = cudaMemcpyAsync(&loss, loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && loss_per_sample_host)
+        e = cudaMemcpyAsync(loss_per_sample_host, loss_out, (end - begin) * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return fail(std::string("training kernel: ") + cudaGetErrorString(e));
+    cudaEventElapsedTime(&c->last_kernel_ms, c->ev0, c->ev1);
+    if (loss_sum_host) *loss_sum_host = loss;
+    return 0;
+}
+
 }  // namespace heat
+
+extern "C" int heat_train_range_noalloc(heat_ctx *ctx, uint64_t begin, uint64_t end, double *loss_sum, float *loss_per_sample)
+{
+    heat::Ctx *c = reinterpret_cast<heat::Ctx *>(ctx);
+    if (!c) return heat::fail("heat_train_range_noalloc: null context");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    return heat::launch_train_noalloc(c, begin, end, loss_sum, loss_per_sample);
+}

@@ -115,6 +115,17 @@ int heat_train_epoch(heat_ctx *ctx, double *mean_loss);
  * host array of (end-begin) floats. */
 int heat_train_range(heat_ctx *ctx, uint64_t begin, uint64_t end, double *loss_sum,
                      float *loss_per_sample);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same contract and same
+ * kernels as heat_train_range, but the call allocates nothing: the chunk counter, the loss sum and the per-sample loss
+ * staging live in ONE file-scope `static __device__` array of the library (train_launch.cu; 256 B +
+ * 4 B x HEAT_NOALLOC_MAX_SAMPLES = 4 MiB held by every GPU that loads the library until exit).  A range of more than
+ * HEAT_NOALLOC_MAX_SAMPLES samples is refused with an error (split it).  All calls on one device share the array, so two
+ * calls that overlap on the GPU (different contexts / host threads) race; the words that must start at zero are cleared
+ * by every call.  The first call on a device looks the array's device address up (cudaGetSymbolAddress). */
+#define HEAT_NOALLOC_MAX_SAMPLES (1u << 20)
+int heat_train_range_noalloc(heat_ctx *ctx, uint64_t begin, uint64_t end, double *loss_sum,
+                             float *loss_per_sample);
 int heat_zero_grad(heat_ctx *ctx);                       /* embedding.cpp:41-45 */
 int heat_get_grads(heat_ctx *ctx, float *user_g, float *item_g);   /* either may be NULL */
 int heat_set_lr(heat_ctx *ctx, float l_r);
