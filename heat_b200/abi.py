@@ -30,7 +30,8 @@ SYMBOLS = [
     "heat_philox_draw", "heat_eval_dense", "heat_eval_topk", "heat_eval_metrics", "heat_last_eval_ms",
     "heat_comm_unique_id", "heat_comm_init", "heat_comm_sync_items", "heat_set_sync_interval", "heat_comm_allreduce_f64",
     "heat_probe_l2_bandwidth", "heat_host_alloc", "heat_host_free", "heat_save_state", "heat_load_state", "heat_clickfile_open", "heat_clickfile_read", "heat_clickfile_close", "heat_tile_draw", "heat_last_engine", "heat_comm_mode",
-    "heat_train_range_noalloc",
+    "heat_train_range_noalloc", "heat_last_exchange", "heat_local_group_init", "heat_local_group_train_epoch",
+    "heat_local_group_share", "heat_probe_tf32_peak",
 ]
 
 
@@ -45,7 +46,7 @@ class HeatConfig(C.Structure):
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
         ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
         ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("engine", C.c_uint32), ("max_blocks", C.c_uint32),
-        ("exchange_mode", C.c_uint32), ("tile_sampler", C.c_uint32),
+        ("exchange_mode", C.c_uint32), ("tile_sampler", C.c_uint32), ("sync_grads", C.c_uint32), ("reserved0", C.c_uint32),
     ]
 
 
@@ -105,8 +106,13 @@ def lib():
         L.heat_comm_sync_items.argtypes = [C.c_void_p]
         L.heat_comm_mode.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         L.heat_set_sync_interval.argtypes = [C.c_void_p, C.c_uint64]
+        L.heat_last_exchange.argtypes = [C.c_void_p, _u64p, _f32p]
+        L.heat_local_group_init.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+        L.heat_local_group_train_epoch.argtypes = [C.POINTER(C.c_void_p), C.c_int, _f64p]
+        L.heat_local_group_share.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_uint32]
         L.heat_comm_allreduce_f64.argtypes = [C.c_void_p, _f64p, C.c_int]
         L.heat_probe_l2_bandwidth.argtypes = [C.c_int, C.c_uint64, C.c_int, _f64p]
+        L.heat_probe_tf32_peak.argtypes = [C.c_int, C.c_int, _f64p]
         L.heat_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
         L.heat_host_free.argtypes = [C.c_void_p]
         _lib = L
@@ -149,6 +155,13 @@ def probe_l2_bandwidth(device=0, nbytes=74 << 20, iters=200):
     return g.value
 
 
+def probe_tf32_peak(device=0, iters=4000):
+    """Measured dense TF32 tcgen05.mma peak of the device, TFLOP/s (heat_probe_tf32_peak)."""
+    g = C.c_double()
+    _ck(lib().heat_probe_tf32_peak(device, iters, C.byref(g)))
+    return g.value
+
+
 def parse_clickfile(path, separator=" "):
     """LightGCN-format file -> (row_users int64 [R], row_indptr int64 [R+1], items int64 [nnz]) in file order,
     parsed natively with one thread per core (heat_clickfile_*; host code, needs no GPU)."""
@@ -178,7 +191,7 @@ class Context:
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
                  warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, history_mode=0, engine=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
-                 tile_sampler=0, exchange_mode=0, device=0):
+                 tile_sampler=0, exchange_mode=0, sync_grads=0, device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
                          train_size=0, neg_sampler=neg_sampler, tile_size=tile_size,
@@ -188,7 +201,7 @@ class Context:
                          w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
                          max_blocks=max_blocks, update_mode=update_mode,
                          sync_average=sync_average, history_mode=history_mode, engine=engine, tile_sampler=tile_sampler,
-                         exchange_mode=exchange_mode)
+                         exchange_mode=exchange_mode, sync_grads=sync_grads)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0
@@ -347,3 +360,25 @@ class Context:
 
     def set_sync_interval(self, samples):
         _ck(lib().heat_set_sync_interval(self._h, samples))
+
+    def last_exchange(self):
+        """(exchanges of the last epoch, their total device time in ms)"""
+        n, ms = C.c_uint64(), C.c_float()
+        _ck(lib().heat_last_exchange(self._h, C.byref(n), C.byref(ms)))
+        return n.value, ms.value
+
+
+class LocalGroup:
+    """n contexts on one device trained as n ranks would be (heat_local_group_*): rank r = ctxs[r] holds shard r."""
+
+    def __init__(self, ctxs, share=0):
+        self.ctxs = list(ctxs)
+        self._arr = (C.c_void_p * len(self.ctxs))(*[c._h for c in self.ctxs])
+        _ck(lib().heat_local_group_init(self._arr, len(self.ctxs)))
+        if share:       # experiment knob: bit 0 W0, bit 1 item grad rows, bit 2 item table held ONCE for all members
+            _ck(lib().heat_local_group_share(self._arr, len(self.ctxs), share))
+
+    def train_epoch(self):
+        loss = C.c_double()
+        _ck(lib().heat_local_group_train_epoch(self._arr, len(self.ctxs), C.byref(loss)))
+        return loss.value

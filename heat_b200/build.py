@@ -14,7 +14,7 @@ import sysconfig
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libheat_b200.so")
-CUDA_SOURCES = ["heat_abi.cu", "train_launch.cu", "train_launch_tile.cu", "train_bigk.cu", "probe.cu", "eval_kernel.cu", "comm.cu", "ingest.cu"]
+CUDA_SOURCES = ["heat_abi.cu", "train_launch.cu", "train_launch_tile.cu", "train_bigk.cu", "probe.cu", "probe_tf32.cu", "eval_kernel.cu", "comm.cu", "ingest.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -81,13 +81,15 @@ __global__ void delta_kernel(const float4 *__restrict__ w, const float4 *__restr
         delta[i] = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
     }
 }
-// base += scale * delta_sum;  w = base
-__global__ void apply_kernel(float4 *__restrict__ w, float4 *__restrict__ base, const float4 *__restrict__ delta, float scale, size_t n4)
+__device__ __forceinline__ float clampc(float v, float c) { return fmaxf(fminf(v, c), -c); }
+// base += scale * delta_sum (clamped to +-clip when clip > 0: the persistent grad rows);  w = base
+__global__ void apply_kernel(float4 *__restrict__ w, float4 *__restrict__ base, const float4 *__restrict__ delta, float scale, float clip, size_t n4)
 {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
         const float4 d = delta[i];
         float4 b = base[i];
         b.x = fmaf(scale, d.x, b.x); b.y = fmaf(scale, d.y, b.y); b.z = fmaf(scale, d.z, b.z); b.w = fmaf(scale, d.w, b.w);
+        if (clip > 0.f) { b.x = clampc(b.x, clip); b.y = clampc(b.y, clip); b.z = clampc(b.z, clip); b.w = clampc(b.w, clip); }
         base[i] = b;
         w[i] = b;
     }
@@ -97,8 +99,11 @@ __global__ void apply_kernel(float4 *__restrict__ w, float4 *__restrict__ base, 
 constexpr int MAX_PEERS = 8;
 struct PeerSync {
     int rank, world;
+    int slice, slices;                             // this launch reduces rows [slice/slices, (slice+1)/slices) of every array
     float4 *w[MAX_PEERS], *base[MAX_PEERS];        // item table / base copy of every rank (peer-mapped; [rank] = local)
     float4 *w0[MAX_PEERS], *w0b[MAX_PEERS];
+    float4 *g[MAX_PEERS], *gb[MAX_PEERS];          // sync_grads: persistent item grad rows / their base copy (null = off)
+    float clip;                                    // the grad rows are clamped to +-clip after the reduction
     unsigned long long *flags[MAX_PEERS];          // [2][8] arrival counters of every rank
     unsigned long long seq;                        // this exchange's number (1, 2, ...)
     float scale;
@@ -146,10 +151,10 @@ __device__ __forceinline__ void peer_barrier(const PeerSync &S, int which)
     __syncthreads();
 }
 
-__device__ __forceinline__ void peer_reduce_range(const PeerSync &S, float4 *const *w, float4 *const *base, size_t n4)
+__device__ __forceinline__ void peer_reduce_range(const PeerSync &S, float4 *const *w, float4 *const *base, size_t n4, float clip)
 {
-    const size_t per = (n4 + S.world - 1) / S.world;
-    const size_t lo = per * S.rank, hi = lo + per < n4 ? lo + per : n4;
+    const size_t per = (n4 + S.slices - 1) / S.slices;
+    const size_t lo = per * S.slice, hi = lo + per < n4 ? lo + per : n4;
     for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
         const float4 b = base[S.rank][i];
         float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -159,8 +164,18 @@ __device__ __forceinline__ void peer_reduce_range(const PeerSync &S, float4 *con
         }
         float4 nb;
         nb.x = fmaf(S.scale, d.x, b.x); nb.y = fmaf(S.scale, d.y, b.y); nb.z = fmaf(S.scale, d.z, b.z); nb.w = fmaf(S.scale, d.w, b.w);
+        if (clip > 0.f) { nb.x = clampc(nb.x, clip); nb.y = clampc(nb.y, clip); nb.z = clampc(nb.z, clip); nb.w = clampc(nb.w, clip); }
         for (int q = 0; q < S.world; ++q) { st_sys4(w[q] + i, nb); st_sys4(base[q] + i, nb); }
     }
+}
+
+// Single-device emulation group (heat_local_group_*): all replicas are plain device pointers of this GPU, one launch
+// reduces every row of every array; same arithmetic and rank order as peer_sync_kernel / the NCCL path.
+__global__ void __launch_bounds__(256) local_sync_kernel(const PeerSync S)
+{
+    if (S.w[0]) peer_reduce_range(S, S.w, S.base, S.n4_items, 0.f);
+    if (S.w0[0]) peer_reduce_range(S, S.w0, S.w0b, S.n4_w0, 0.f);
+    if (S.g[0]) peer_reduce_range(S, S.g, S.gb, S.n4_items, S.clip);
 }
 
 __global__ void __launch_bounds__(256) peer_sync_kernel(const PeerSync S)
@@ -174,8 +189,9 @@ __global__ void __launch_bounds__(256) peer_sync_kernel(const PeerSync S)
         if (threadIdx.x == 0) while (ld_acquire_gpu(S.grid_sync) != seq32) { }
         __syncthreads();
     }
-    peer_reduce_range(S, S.w, S.base, S.n4_items);
-    peer_reduce_range(S, S.w0, S.w0b, S.n4_w0);
+    peer_reduce_range(S, S.w, S.base, S.n4_items, 0.f);
+    peer_reduce_range(S, S.w0, S.w0b, S.n4_w0, 0.f);
+    if (S.g[0]) peer_reduce_range(S, S.g, S.gb, S.n4_items, S.clip);
     // end barrier: my stores have landed in every replica and every peer's stores have landed in mine before any
     // later kernel of this stream starts; the last block to finish carries it
     __threadfence_system();
@@ -194,11 +210,13 @@ int peer_setup(Ctx *c, NcclApi *api)
     HEAT_CUDA(cudaMemset(c->xflags, 0, 2 * MAX_PEERS * sizeof(unsigned long long)));
     HEAT_CUDA(cudaMalloc(&c->grid_sync, 2 * sizeof(unsigned)));
     HEAT_CUDA(cudaMemset(c->grid_sync, 0, 2 * sizeof(unsigned)));
-    struct Export { cudaIpcMemHandle_t h[5]; int ok; int pad[15]; };
+    constexpr int NH = 7;
+    struct Export { cudaIpcMemHandle_t h[NH]; int ok; int pad[15]; };
     Export mine{};
-    void *ptrs[5] = {c->item_w, c->item_base, c->w0, c->w0_base, c->xflags};
+    void *ptrs[NH] = {c->item_w, c->item_base, c->w0, c->w0_base, c->xflags, c->item_g, c->item_g_base};
+    const int nh = c->item_g_base ? NH : 5;        // the grad rows travel only with sync_grads
     mine.ok = 1;
-    for (int i = 0; i < 5; ++i)
+    for (int i = 0; i < nh; ++i)
         if (cudaIpcGetMemHandle(&mine.h[i], ptrs[i]) != cudaSuccess) { mine.ok = 0; cudaGetLastError(); }
     Export *d_all = nullptr;
     HEAT_CUDA(cudaMalloc(&d_all, sizeof(Export) * c->world));
@@ -211,14 +229,15 @@ int peer_setup(Ctx *c, NcclApi *api)
     bool ok = true;
     for (int q = 0; q < c->world; ++q) ok = ok && all[q].ok;
     for (int q = 0; q < c->world && ok; ++q) {
-        void *m[5];
+        void *m[NH] = {};
         if (q == c->rank) {
-            for (int i = 0; i < 5; ++i) m[i] = ptrs[i];
+            for (int i = 0; i < nh; ++i) m[i] = ptrs[i];
         } else {
-            for (int i = 0; i < 5 && ok; ++i)
+            for (int i = 0; i < nh && ok; ++i)
                 if (cudaIpcOpenMemHandle(&m[i], all[q].h[i], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = false; cudaGetLastError(); }
         }
         if (!ok) break;
+        c->peer_item_g[q] = static_cast<float *>(m[5]); c->peer_item_g_base[q] = static_cast<float *>(m[6]);
         c->peer_item_w[q] = static_cast<float *>(m[0]); c->peer_item_base[q] = static_cast<float *>(m[1]);
         c->peer_w0[q] = static_cast<float *>(m[2]); c->peer_w0_base[q] = static_cast<float *>(m[3]);
         c->peer_flags[q] = static_cast<unsigned long long *>(m[4]);
@@ -236,12 +255,14 @@ int peer_setup(Ctx *c, NcclApi *api)
 int peer_sync(Ctx *c)
 {
     PeerSync S{};
-    S.rank = c->rank; S.world = c->world;
+    S.rank = c->rank; S.world = c->world; S.slice = c->rank; S.slices = c->world;
     for (int q = 0; q < c->world; ++q) {
         S.w[q] = reinterpret_cast<float4 *>(c->peer_item_w[q]); S.base[q] = reinterpret_cast<float4 *>(c->peer_item_base[q]);
         S.w0[q] = reinterpret_cast<float4 *>(c->peer_w0[q]); S.w0b[q] = reinterpret_cast<float4 *>(c->peer_w0_base[q]);
+        S.g[q] = reinterpret_cast<float4 *>(c->peer_item_g[q]); S.gb[q] = reinterpret_cast<float4 *>(c->peer_item_g_base[q]);
         S.flags[q] = c->peer_flags[q];
     }
+    S.clip = c->cfg.clip_val;
     const size_t D = c->cfg.emb_dim;
     S.seq = c->syncs + 1;
     S.scale = c->cfg.sync_average ? 1.0f / (float)c->world : 1.0f;
@@ -276,6 +297,7 @@ int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128])
     if (world < 1 || rank < 0 || rank >= world) return fail("heat_comm_init: bad rank/world");
     if (!c->item_w) return fail("heat_comm_init: bind the tables first");
     if (c->nccl_comm) return fail("heat_comm_init: already initialised");
+    if (c->local_group) return fail("heat_comm_init: the context belongs to a local emulation group");
     ncclUniqueId id;
     std::memcpy(&id, uid, 128);
     ncclComm_t comm;
@@ -285,7 +307,11 @@ int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128])
     const size_t D = c->cfg.emb_dim, ib = c->cfg.num_items * D * sizeof(float), wb = D * D * sizeof(float);
     HEAT_CUDA(cudaMalloc(&c->item_base, ib));
     HEAT_CUDA(cudaMalloc(&c->w0_base, wb));
-    HEAT_CUDA(cudaMalloc(&c->delta, ib + wb));      // item delta followed by the W0 delta: one all-reduce
+    if (c->cfg.sync_grads) {
+        HEAT_CUDA(cudaMalloc(&c->item_g_base, ib));
+        HEAT_CUDA(cudaMemcpyAsync(c->item_g_base, c->item_g, ib, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    HEAT_CUDA(cudaMalloc(&c->delta, ib + wb + (c->cfg.sync_grads ? ib : 0)));      // [item delta | W0 delta | grad-row delta]: one all-reduce
     HEAT_CUDA(cudaMalloc(&c->loss_pair, 2 * sizeof(double)));
     HEAT_CUDA(cudaMemcpyAsync(c->item_base, c->item_w, ib, cudaMemcpyDeviceToDevice, c->stream));
     HEAT_CUDA(cudaMemcpyAsync(c->w0_base, c->w0, wb, cudaMemcpyDeviceToDevice, c->stream));
@@ -304,14 +330,83 @@ int comm_sync_items(Ctx *c)
     const int blocks = c->num_sms * 8;
     delta_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->item_w), reinterpret_cast<const float4 *>(c->item_base), delta, in4);
     delta_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->w0), reinterpret_cast<const float4 *>(c->w0_base), delta + in4, wn4);
+    const size_t gn4 = c->item_g_base ? in4 : 0;
+    if (gn4) delta_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->item_g), reinterpret_cast<const float4 *>(c->item_g_base), delta + in4 + wn4, gn4);
     HEAT_CUDA(cudaGetLastError());
-    HEAT_NCCL(api->AllReduce(c->delta, c->delta, (in4 + wn4) * 4, ncclFloat, ncclSum, static_cast<ncclComm_t>(c->nccl_comm), c->stream));
+    HEAT_NCCL(api->AllReduce(c->delta, c->delta, (in4 + wn4 + gn4) * 4, ncclFloat, ncclSum, static_cast<ncclComm_t>(c->nccl_comm), c->stream));
     const float scale = c->cfg.sync_average ? 1.0f / (float)c->world : 1.0f;
-    apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_w), reinterpret_cast<float4 *>(c->item_base), delta, scale, in4);
-    apply_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->w0), reinterpret_cast<float4 *>(c->w0_base), delta + in4, scale, wn4);
+    apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_w), reinterpret_cast<float4 *>(c->item_base), delta, scale, 0.f, in4);
+    apply_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->w0), reinterpret_cast<float4 *>(c->w0_base), delta + in4, scale, 0.f, wn4);
+    if (gn4) apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_g), reinterpret_cast<float4 *>(c->item_g_base), delta + in4 + wn4, scale, c->cfg.clip_val, gn4);
     HEAT_CUDA(cudaGetLastError());
-    c->launches += 4;
+    c->launches += gn4 ? 6 : 4;
     c->syncs += 1;
+    return 0;
+}
+
+// ---- single-device emulation group ---------------------------------------------------------------------------
+int local_group_init(Ctx **cs, int n)
+{
+    if (n < 1 || n > MAX_PEERS) return fail("heat_local_group_init: 1..8 contexts");
+    for (int q = 0; q < n; ++q) {
+        Ctx *c = cs[q];
+        if (!c || !c->item_w) return fail("heat_local_group_init: bind the tables of every context first");
+        if (c->nccl_comm) return fail("heat_local_group_init: a context already has a communicator");
+        if (c->device != cs[0]->device || c->cfg.emb_dim != cs[0]->cfg.emb_dim || c->cfg.num_items != cs[0]->cfg.num_items)
+            return fail("heat_local_group_init: the contexts must share device, emb_dim and num_items");
+    }
+    const size_t D = cs[0]->cfg.emb_dim, ib = cs[0]->cfg.num_items * D * sizeof(float), wb = D * D * sizeof(float);
+    for (int q = 0; q < n; ++q) {
+        Ctx *c = cs[q];
+        if (!c->item_base) { HEAT_CUDA(cudaMalloc(&c->item_base, ib)); HEAT_CUDA(cudaMalloc(&c->w0_base, wb)); }
+        if (cs[0]->cfg.sync_grads && !c->item_g_base) HEAT_CUDA(cudaMalloc(&c->item_g_base, ib));
+        HEAT_CUDA(cudaMemcpyAsync(c->item_base, c->item_w, ib, cudaMemcpyDeviceToDevice, c->stream));
+        HEAT_CUDA(cudaMemcpyAsync(c->w0_base, c->w0, wb, cudaMemcpyDeviceToDevice, c->stream));
+        if (c->item_g_base) HEAT_CUDA(cudaMemcpyAsync(c->item_g_base, c->item_g, ib, cudaMemcpyDeviceToDevice, c->stream));
+        HEAT_CUDA(cudaStreamSynchronize(c->stream));
+        c->local_group = true; c->rank = q; c->world = n;
+    }
+    return 0;
+}
+
+int local_group_share(Ctx **cs, int n, uint32_t mask)
+{
+    for (int q = 0; q < n; ++q)
+        if (!cs[q] || !cs[q]->local_group) return fail("heat_local_group_share: call heat_local_group_init first");
+    if (cs[0]->group_shared) return fail("heat_local_group_share: already shared");
+    for (int q = 1; q < n; ++q) {
+        Ctx *c = cs[q];
+        if (mask & 1u) { cudaFree(c->w0); c->w0 = cs[0]->w0; }
+        if (mask & 2u) { cudaFree(c->item_g); c->item_g = cs[0]->item_g; }
+        if (mask & 4u) { cudaFree(c->item_w); c->item_w = cs[0]->item_w; }
+        c->shared_mask = mask;
+    }
+    for (int q = 0; q < n; ++q) cs[q]->group_shared = mask;
+    return 0;
+}
+
+// all member streams are idle when this is called (heat_local_group_train_epoch synchronises them); runs on cs[0]'s stream
+int local_group_sync(Ctx **cs, int n)
+{
+    Ctx *c0 = cs[0];
+    PeerSync S{};
+    S.rank = 0; S.world = n; S.slice = 0; S.slices = 1;
+    const uint32_t sh = c0->group_shared;          // arrays the members share physically need no reconciliation
+    const bool grads = c0->cfg.sync_grads && !(sh & 2u);
+    for (int q = 0; q < n; ++q) {
+        S.w[q] = (sh & 4u) ? nullptr : reinterpret_cast<float4 *>(cs[q]->item_w); S.base[q] = reinterpret_cast<float4 *>(cs[q]->item_base);
+        S.w0[q] = (sh & 1u) ? nullptr : reinterpret_cast<float4 *>(cs[q]->w0); S.w0b[q] = reinterpret_cast<float4 *>(cs[q]->w0_base);
+        S.g[q] = grads ? reinterpret_cast<float4 *>(cs[q]->item_g) : nullptr;
+        S.gb[q] = grads ? reinterpret_cast<float4 *>(cs[q]->item_g_base) : nullptr;
+    }
+    const size_t D = c0->cfg.emb_dim;
+    S.scale = c0->cfg.sync_average ? 1.0f / (float)n : 1.0f;
+    S.clip = c0->cfg.clip_val;
+    S.n4_items = c0->cfg.num_items * D / 4; S.n4_w0 = D * D / 4;
+    local_sync_kernel<<<c0->num_sms * 4, 256, 0, c0->stream>>>(S);
+    HEAT_CUDA(cudaGetLastError());
+    c0->launches += 1;
+    for (int q = 0; q < n; ++q) cs[q]->syncs += 1;
     return 0;
 }
 
@@ -372,12 +467,14 @@ void comm_destroy(Ctx *c)
     if (c->peer_ok) {
         for (int q = 0; q < c->world; ++q) {
             if (q == c->rank) continue;
+            if (c->peer_item_g[q]) { cudaIpcCloseMemHandle(c->peer_item_g[q]); cudaIpcCloseMemHandle(c->peer_item_g_base[q]); }
             cudaIpcCloseMemHandle(c->peer_item_w[q]); cudaIpcCloseMemHandle(c->peer_item_base[q]);
             cudaIpcCloseMemHandle(c->peer_w0[q]); cudaIpcCloseMemHandle(c->peer_w0_base[q]); cudaIpcCloseMemHandle(c->peer_flags[q]);
         }
         c->peer_ok = false;
     }
-    cudaFree(c->delta); cudaFree(c->loss_pair); cudaFree(c->xflags); cudaFree(c->grid_sync);
+    cudaFree(c->delta); cudaFree(c->loss_pair); cudaFree(c->xflags); cudaFree(c->grid_sync); cudaFree(c->item_g_base);
+    c->item_g_base = nullptr;
     c->delta = nullptr; c->loss_pair = nullptr; c->xflags = nullptr; c->grid_sync = nullptr;
 }
 

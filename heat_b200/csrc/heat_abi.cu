@@ -58,6 +58,10 @@ void free_dataset(Ctx *c)
 }
 void free_tables(Ctx *c)
 {
+    // arrays borrowed from member 0 of an emulation group (heat_local_group_share) are not this context's to free
+    if (c->shared_mask & 1u) c->w0 = nullptr;
+    if (c->shared_mask & 2u) c->item_g = nullptr;
+    if (c->shared_mask & 4u) c->item_w = nullptr;
     cudaFree(c->user_w); cudaFree(c->item_w); cudaFree(c->user_g); cudaFree(c->item_g); cudaFree(c->w0);
     cudaFree(c->item_base); cudaFree(c->w0_base);
     c->user_w = c->item_w = c->user_g = c->item_g = c->w0 = c->item_base = c->w0_base = nullptr;
@@ -137,6 +141,7 @@ int heat_destroy(heat_ctx *ctx)
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_e0) cudaEventDestroy(c->ev_e0);
     if (c->ev_e1) cudaEventDestroy(c->ev_e1);
+    for (cudaEvent_t e : c->seg_ev) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return 0;
@@ -158,6 +163,7 @@ int heat_set_dataset(heat_ctx *ctx, const uint64_t *clicks, uint64_t n, const ui
     if (int rc = grow(&c->masks, &c->masks_cap, (size_t)num_users)) return rc;
     if (int rc = grow(&c->stage, &c->stage_cap, n_ids + 2)) return rc;
     c->n_samples = n; c->max_his = max_his; c->cfg.train_size = n;
+    c->nmax_for = ~0ull;                                // the largest shard over the ranks is agreed on again
     int *bad = reinterpret_cast<int *>(c->stage + n_ids);
     HEAT_CUDA(cudaMemsetAsync(bad, 0, 3 * sizeof(int), c->stream));
     if (int rc = queue_narrow(c, clicks, 2 * n, c->stage, reinterpret_cast<int *>(c->clicks), c->cfg.num_users, c->cfg.num_items, bad)) return rc;
@@ -179,6 +185,8 @@ int heat_bind_tables(heat_ctx *ctx, float *user_w, float *item_w, float *w0)
 {
     Ctx *c = reinterpret_cast<Ctx *>(ctx);
     if (!c || !user_w || !item_w || !w0) return fail("heat_bind_tables: null argument");
+    if (c->nccl_comm || c->local_group)
+        return fail("heat_bind_tables: the tables are already shared with other ranks (peers hold mappings of them); create a new context");
     HEAT_CUDA(cudaSetDevice(c->device));
     free_tables(c);
     const size_t D = c->cfg.emb_dim, ub = c->cfg.num_users * D * sizeof(float), ib = c->cfg.num_items * D * sizeof(float);
@@ -229,6 +237,7 @@ int heat_zero_grad(heat_ctx *ctx)
     const size_t D = c->cfg.emb_dim;
     HEAT_CUDA(cudaMemsetAsync(c->user_g, 0, c->cfg.num_users * D * sizeof(float), c->stream));
     HEAT_CUDA(cudaMemsetAsync(c->item_g, 0, c->cfg.num_items * D * sizeof(float), c->stream));
+    if (c->item_g_base) HEAT_CUDA(cudaMemsetAsync(c->item_g_base, 0, c->cfg.num_items * D * sizeof(float), c->stream));
     return 0;
 }
 
@@ -240,50 +249,180 @@ int heat_train_range(heat_ctx *ctx, uint64_t begin, uint64_t end, double *loss_s
     return launch_train(c, begin, end, loss_sum, loss_per_sample);
 }
 
-int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
+namespace {
+
+// LR schedule, engine.cpp:156-160 -> optimizer.cpp:24-38 (decay 0.1)
+void lr_schedule(Ctx *c)
 {
-    Ctx *c = reinterpret_cast<Ctx *>(ctx);
-    if (!c) return fail("heat_train_epoch: null context");
-    HEAT_CUDA(cudaSetDevice(c->device));
-    // LR schedule, engine.cpp:156-160 -> optimizer.cpp:24-38 (decay 0.1)
     if (c->milestones.size() > 1) {
         for (uint64_t m : c->milestones)
             if (m == c->epoch) { c->l_r = c->l_r * 0.1f; break; }
     } else if (c->milestones.size() == 1 && c->milestones[0] != 0) {
         if (c->epoch > 0 && c->epoch % c->milestones[0] == 0) c->l_r = c->l_r * 0.1f;
     }
+}
+
+int need_seg_events(Ctx *c, uint64_t nseg)
+{
+    while (c->seg_ev.size() < 3 * nseg) {
+        cudaEvent_t e = nullptr;
+        HEAT_CUDA(cudaEventCreate(&e));
+        c->seg_ev.push_back(e);
+    }
+    return 0;
+}
+
+// segment i of nseg over N local samples
+inline void seg_range(uint64_t N, uint64_t i, uint64_t nseg, uint64_t *b, uint64_t *e)
+{
+    *b = (uint64_t)((unsigned __int128)N * i / nseg);
+    *e = (uint64_t)((unsigned __int128)N * (i + 1) / nseg);
+}
+
+// device times of the epoch just synchronised: training kernels and exchanges, from the segment events
+void seg_times(Ctx *c, uint64_t nseg, bool exchanged)
+{
+    float k = 0.f, x = 0.f, t = 0.f;
+    for (uint64_t i = 0; i < nseg; ++i) {
+        if (cudaEventElapsedTime(&t, c->seg_ev[3 * i], c->seg_ev[3 * i + 1]) == cudaSuccess) k += t;
+        if (exchanged && cudaEventElapsedTime(&t, c->seg_ev[3 * i + 1], c->seg_ev[3 * i + 2]) == cudaSuccess) x += t;
+    }
+    c->last_kernel_ms = k; c->last_exchange_ms = x; c->last_exchanges = exchanged ? nseg : 0;
+}
+
+}  // namespace
+
+int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_train_epoch: null context");
+    if (c->local_group) return fail("heat_train_epoch: the context belongs to a local emulation group (heat_local_group_train_epoch)");
+    HEAT_CUDA(cudaSetDevice(c->device));
+    lr_schedule(c);
     const uint64_t N = c->n_samples;
-    HEAT_CUDA(cudaEventRecord(c->ev_e0, c->stream));
-    double total = 0.0;
-    float ms_total = 0.f;
     // Multi-GPU: every rank runs the same number of segments (a collective follows each one), so
     // the count comes from the largest shard; a rank's segment i is its own [N*i/nseg, N*(i+1)/nseg).
     uint64_t nseg = 1;
     if (c->world > 1 && c->sync_interval) {
-        uint64_t nmax = N;
-        int rc = comm_max_u64(c, &nmax);
-        if (rc) return rc;
-        nseg = std::max<uint64_t>(1, (nmax + c->sync_interval - 1) / c->sync_interval);
+        if (c->nmax_for != N) {
+            uint64_t nmax = N;
+            int rc = comm_max_u64(c, &nmax);
+            if (rc) return rc;
+            c->nmax = nmax; c->nmax_for = N;
+        }
+        nseg = std::max<uint64_t>(1, (c->nmax + c->sync_interval - 1) / c->sync_interval);
     }
+    if (int rc = need_seg_events(c, nseg)) return rc;
+    // The whole epoch is queued on the stream -- segments and exchanges back to back -- and synchronised once: the
+    // loss accumulates on the device and is read at the end.
+    HEAT_CUDA(cudaEventRecord(c->ev_e0, c->stream));
+    HEAT_CUDA(cudaMemsetAsync(c->loss_sum, 0, sizeof(double), c->stream));
     for (uint64_t i = 0; i < nseg; ++i) {
-        const uint64_t b = (uint64_t)((unsigned __int128)N * i / nseg), e = (uint64_t)((unsigned __int128)N * (i + 1) / nseg);
-        double part = 0.0;
-        int rc = launch_train(c, b, e, &part, nullptr);
+        uint64_t b, e;
+        seg_range(N, i, nseg, &b, &e);
+        HEAT_CUDA(cudaEventRecord(c->seg_ev[3 * i], c->stream));
+        int rc = queue_train(c, b, e);
         if (rc) return rc;
-        total += part; ms_total += c->last_kernel_ms;
-        if (c->world > 1) { rc = comm_sync_items(c); if (rc) return rc; }
+        HEAT_CUDA(cudaEventRecord(c->seg_ev[3 * i + 1], c->stream));
+        if (c->world > 1) {
+            rc = comm_sync_items(c);
+            if (rc) return rc;
+            HEAT_CUDA(cudaEventRecord(c->seg_ev[3 * i + 2], c->stream));
+        }
     }
-    c->last_kernel_ms = ms_total;
     int rc = heat_zero_grad(ctx);                       // engine.cpp:345-347
     if (rc) return rc;
+    double total = 0.0;
+    HEAT_CUDA(cudaMemcpyAsync(&total, c->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     HEAT_CUDA(cudaEventRecord(c->ev_e1, c->stream));
-    HEAT_CUDA(cudaStreamSynchronize(c->stream));
+    cudaError_t se = cudaStreamSynchronize(c->stream);
+    if (se != cudaSuccess) return fail(std::string("training epoch: ") + cudaGetErrorString(se));
     cudaEventElapsedTime(&c->last_epoch_ms, c->ev_e0, c->ev_e1);
+    seg_times(c, nseg, c->world > 1);
     c->epoch += 1;                                      // engine.cpp:378
     double samples = (double)N;
     rc = comm_reduce_loss(c, &total, &samples);         // engine.cpp:380-383
     if (rc) return rc;
     if (mean_loss) *mean_loss = samples > 0 ? total / samples : 0.0;
+    return 0;
+}
+
+int heat_local_group_init(heat_ctx **ctxs, int n)
+{
+    if (!ctxs || n < 1) return fail("heat_local_group_init: bad argument");
+    Ctx **cs = reinterpret_cast<Ctx **>(ctxs);
+    if (!cs[0]) return fail("heat_local_group_init: null context");
+    HEAT_CUDA(cudaSetDevice(cs[0]->device));
+    return local_group_init(cs, n);
+}
+
+int heat_local_group_train_epoch(heat_ctx **ctxs, int n, double *mean_loss)
+{
+    if (!ctxs || n < 1 || n > 8) return fail("heat_local_group_train_epoch: bad argument");
+    Ctx **cs = reinterpret_cast<Ctx **>(ctxs);
+    for (int q = 0; q < n; ++q)
+        if (!cs[q] || !cs[q]->local_group || cs[q]->world != n || cs[q]->rank != q)
+            return fail("heat_local_group_train_epoch: not the group heat_local_group_init was called with");
+    Ctx *c0 = cs[0];
+    HEAT_CUDA(cudaSetDevice(c0->device));
+    uint64_t nmax = 0, total_n = 0;
+    for (int q = 0; q < n; ++q) { lr_schedule(cs[q]); nmax = std::max(nmax, cs[q]->n_samples); total_n += cs[q]->n_samples; }
+    const uint64_t nseg = c0->sync_interval ? std::max<uint64_t>(1, (nmax + c0->sync_interval - 1) / c0->sync_interval) : 1;
+    if (int rc = need_seg_events(c0, nseg)) return rc;
+    for (int q = 0; q < n; ++q) HEAT_CUDA(cudaMemsetAsync(cs[q]->loss_sum, 0, sizeof(double), cs[q]->stream));
+    float k_ms = 0.f, x_ms = 0.f;
+    for (uint64_t i = 0; i < nseg; ++i) {
+        for (int q = 0; q < n; ++q) {                   // "ranks" one after the other: replicas are independent between exchanges
+            uint64_t b, e;
+            seg_range(cs[q]->n_samples, i, nseg, &b, &e);
+            HEAT_CUDA(cudaEventRecord(cs[q]->ev_e0, cs[q]->stream));
+            int rc = queue_train(cs[q], b, e);
+            if (rc) return rc;
+            HEAT_CUDA(cudaEventRecord(cs[q]->ev_e1, cs[q]->stream));
+            HEAT_CUDA(cudaStreamSynchronize(cs[q]->stream));
+            float t = 0.f;
+            cudaEventElapsedTime(&t, cs[q]->ev_e0, cs[q]->ev_e1);
+            if (q == 0) k_ms += t;                      // rank 0's kernels, as a real rank would report
+        }
+        HEAT_CUDA(cudaEventRecord(c0->seg_ev[3 * i + 1], c0->stream));
+        int rc = local_group_sync(cs, n);
+        if (rc) return rc;
+        HEAT_CUDA(cudaEventRecord(c0->seg_ev[3 * i + 2], c0->stream));
+        HEAT_CUDA(cudaStreamSynchronize(c0->stream));
+        float t = 0.f;
+        cudaEventElapsedTime(&t, c0->seg_ev[3 * i + 1], c0->seg_ev[3 * i + 2]);
+        x_ms += t;
+    }
+    double total = 0.0;
+    for (int q = 0; q < n; ++q) {
+        int rc = heat_zero_grad(reinterpret_cast<heat_ctx *>(cs[q]));
+        if (rc) return rc;
+        double part = 0.0;
+        HEAT_CUDA(cudaMemcpyAsync(&part, cs[q]->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, cs[q]->stream));
+        HEAT_CUDA(cudaStreamSynchronize(cs[q]->stream));
+        total += part;
+        cs[q]->epoch += 1;
+        cs[q]->last_kernel_ms = k_ms; cs[q]->last_exchange_ms = x_ms; cs[q]->last_exchanges = nseg;
+    }
+    if (mean_loss) *mean_loss = total_n ? total / (double)total_n : 0.0;
+    return 0;
+}
+
+int heat_local_group_share(heat_ctx **ctxs, int n, uint32_t mask)
+{
+    if (!ctxs || n < 1 || n > 8) return fail("heat_local_group_share: bad argument");
+    Ctx **cs = reinterpret_cast<Ctx **>(ctxs);
+    if (!cs[0]) return fail("heat_local_group_share: null context");
+    HEAT_CUDA(cudaSetDevice(cs[0]->device));
+    return local_group_share(cs, n, mask);
+}
+
+int heat_last_exchange(heat_ctx *ctx, uint64_t *count, float *ms)
+{
+    Ctx *c = reinterpret_cast<Ctx *>(ctx);
+    if (!c) return fail("heat_last_exchange: null context");
+    if (count) *count = c->last_exchanges;
+    if (ms) *ms = c->last_exchange_ms;
     return 0;
 }
 
@@ -513,6 +652,7 @@ int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples)
 }
 
 int heat_probe_l2_bandwidth(int device, uint64_t bytes, int iters, double *gbps) { return probe_l2(device, bytes, iters, gbps); }
+int heat_probe_tf32_peak(int device, int iters, double *tflops) { return probe_tf32(device, iters, tflops); }
 
 int heat_host_alloc(void **ptr, uint64_t bytes)
 {

@@ -33,7 +33,10 @@ struct Ctx {
 
     float l_r = 0.f;          // optimizer LR (scheduled); cfg.l_r stays the aggregator's LR
     uint64_t epoch = 0;
-    float last_kernel_ms = 0.f, last_eval_ms = 0.f, last_epoch_ms = 0.f;
+    float last_kernel_ms = 0.f, last_eval_ms = 0.f, last_epoch_ms = 0.f, last_exchange_ms = 0.f;
+    uint64_t last_exchanges = 0;
+    std::vector<cudaEvent_t> seg_ev;           // 3 events per sync segment of an epoch: train start, train end, exchange end
+    uint64_t nmax_for = ~0ull, nmax = 0;       // largest shard over the ranks (cached per dataset size)
     uint64_t launches = 0;
     int last_engine = 0;      // kernel family of the last training launch: 1 warp per sample, 2 CTA per sample, 3 large-negative
 
@@ -41,11 +44,16 @@ struct Ctx {
     int rank = 0, world = 1;
     void *nccl_comm = nullptr;
     float *item_base = nullptr, *w0_base = nullptr, *delta = nullptr;
+    float *item_g_base = nullptr;              // sync_grads: item grad rows at the last exchange
+    bool local_group = false;                  // member of a single-device emulation group (heat_local_group_init)
+    uint32_t shared_mask = 0;                  // heat_local_group_share: arrays this member borrows from member 0 (not freed here)
+    uint32_t group_shared = 0;                 // ... and the arrays the group shares at all (skipped by the reconciliation)
     double *loss_pair = nullptr;
     uint64_t sync_interval = 0, syncs = 0;
     // fused exchange over NVLink peer memory (comm.cu): every rank's tables and flags mapped through CUDA IPC
     bool peer_ok = false;
     float *peer_item_w[8] = {}, *peer_item_base[8] = {}, *peer_w0[8] = {}, *peer_w0_base[8] = {};
+    float *peer_item_g[8] = {}, *peer_item_g_base[8] = {};
     unsigned long long *peer_flags[8] = {};    // [2][8] arrival counters per rank: [0] start barrier, [1] end barrier
     unsigned long long *xflags = nullptr;      // this rank's flags
     unsigned *grid_sync = nullptr;             // intra-grid release flag and done counter of peer_sync_kernel
@@ -75,6 +83,8 @@ template <class Params> inline void set_sampler(const Ctx *c, Params &P)
 
 // train_launch.cu
 int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host);
+// the same launch queued on the context's stream without any synchronisation; the loss is ADDED to c->loss_sum
+int queue_train(Ctx *c, uint64_t begin, uint64_t end);
 // train_launch_tile.cu: the CTA kernel's hot-tile-sampler instantiations (-1: (emb_dim, num_negs) not covered)
 struct TrainParams;
 int dispatch_cta_tile(Ctx *c, const TrainParams &P, int blocks);
@@ -91,6 +101,9 @@ void eval_free(Ctx *c);
 int comm_unique_id(uint8_t out[128]);
 int comm_init(Ctx *c, int rank, int world, const uint8_t uid[128]);
 int comm_sync_items(Ctx *c);
+int local_group_init(Ctx **cs, int n);
+int local_group_sync(Ctx **cs, int n);
+int local_group_share(Ctx **cs, int n, uint32_t mask);
 int comm_mode(const Ctx *c);
 int comm_reduce_loss(Ctx *c, double *loss_sum, double *samples);
 int comm_allreduce_f64(Ctx *c, double *vals, int n);
@@ -98,5 +111,7 @@ int comm_max_u64(Ctx *c, uint64_t *v);
 void comm_destroy(Ctx *c);
 // probe.cu
 int probe_l2(int device, uint64_t bytes, int iters, double *gbps);
+// probe_tf32.cu
+int probe_tf32(int device, int iters, double *tflops);
 
 }  // namespace heat

@@ -51,7 +51,9 @@ PYBIND11_MODULE(cf_c, cf_module)
         .def_readwrite("history_mode", &CFConfig::history_mode)
         .def_readwrite("engine", &CFConfig::engine)
         .def_readwrite("tile_sampler", &CFConfig::tile_sampler)
-        .def_readwrite("exchange_mode", &CFConfig::exchange_mode);
+        .def_readwrite("exchange_mode", &CFConfig::exchange_mode)
+        .def_readwrite("sync_grads", &CFConfig::sync_grads)
+        .def_readwrite("w0_tail_mode", &CFConfig::w0_tail_mode);
 
     py::module_ datasets = m.def_submodule("datasets", "datasets");
     py::class_<Dataset, std::shared_ptr<Dataset>>(datasets, "Dataset");

@@ -134,24 +134,24 @@ int auto_warp_engine(const Ctx *c, int D, int K)
 
 }  // namespace
 
-int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host)
+namespace {
+
+int check_range(Ctx *c, uint64_t begin, uint64_t end)
 {
     if (!c->clicks) return fail("heat_set_dataset has not been called");
     if (!c->user_w) return fail("heat_bind_tables has not been called");
     if (end > c->n_samples || begin > end) return fail("sample range out of bounds");
     if (c->max_his > 128) return fail("max_his > 128 is not supported by the training kernel");
-    if (loss_sum_host) *loss_sum_host = 0.0;
-    if (begin == end) { c->last_kernel_ms = 0.f; return 0; }
+    return 0;
+}
 
-    float *d_loss_out = nullptr;
-    if (loss_per_sample_host) HEAT_CUDA(cudaMalloc(&d_loss_out, (end - begin) * sizeof(float)));
-    HEAT_CUDA(cudaMemsetAsync(c->chunk_counter, 0, sizeof(unsigned long long), c->stream));
-    HEAT_CUDA(cudaMemsetAsync(c->loss_sum, 0, sizeof(double), c->stream));
-
+// kernel parameter block of local samples [begin,end) with the given scratch words
+TrainParams make_params(Ctx *c, uint64_t begin, uint64_t end, unsigned long long *counter, double *loss_sum, float *loss_out)
+{
     TrainParams P{};
     P.clicks = c->clicks; P.his = c->his; P.masks = c->masks;
     P.user_w = c->user_w; P.item_w = c->item_w; P.user_g = c->user_g; P.item_g = c->item_g; P.w0 = c->w0;
-    P.chunk_counter = c->chunk_counter; P.loss_sum = c->loss_sum; P.loss_out = d_loss_out;
+    P.chunk_counter = counter; P.loss_sum = loss_sum; P.loss_out = loss_out;
     P.begin = (long long)begin; P.end = (long long)end;
     P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed;
     set_sampler(c, P);
@@ -161,8 +161,13 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
     P.upd = (int)c->cfg.update_mode;
     P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
-
     P.no_cache = c->cfg.history_mode == 1;
+    return P;
+}
+
+// engine choice (heat_config.engine, heat_last_engine) and the launch itself, queued on c->stream between ev0 and ev1
+int run_engine(Ctx *c, const TrainParams &P)
+{
     int rc = -1;
     c->last_engine = 0;
     const int auto_w = c->cfg.engine == 0 ? auto_warp_engine(c, (int)c->cfg.emb_dim, P.K) : 0;
@@ -174,9 +179,28 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
         if (c->cfg.engine == 3 || (c->cfg.engine == 0 && !warp_covers((int)c->cfg.emb_dim, P.K))) { rc = dispatch_bigk(c, P, det); c->last_engine = 3; }
         else { rc = dispatch(c, P, det); c->last_engine = 1; }
     }
+    return rc;
+}
+
+}  // namespace
+
+int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host)
+{
+    if (int rc = check_range(c, begin, end)) return rc;
+    if (loss_sum_host) *loss_sum_host = 0.0;
+    if (begin == end) { c->last_kernel_ms = 0.f; return 0; }
+
+    float *d_loss_out = nullptr;
+    if (loss_per_sample_host) HEAT_CUDA(cudaMalloc(&d_loss_out, (end - begin) * sizeof(float)));
+    cudaError_t e = cudaMemsetAsync(c->chunk_counter, 0, sizeof(unsigned long long), c->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(c->loss_sum, 0, sizeof(double), c->stream);
+    if (e != cudaSuccess) { cudaFree(d_loss_out); return fail(std::string("training launch: ") + cudaGetErrorString(e)); }
+
+    const TrainParams P = make_params(c, begin, end, c->chunk_counter, c->loss_sum, d_loss_out);
+    int rc = run_engine(c, P);
     if (rc == 0) {
         double loss = 0.0;
-        cudaError_t e = cudaMemcpyAsync(&loss, c->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+        e = cudaMemcpyAsync(&loss, c->loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
         if (e == cudaSuccess && loss_per_sample_host)
             e = cudaMemcpyAsync(loss_per_sample_host, d_loss_out, (end - begin) * sizeof(float),
                                 cudaMemcpyDeviceToHost, c->stream);
@@ -191,6 +215,16 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     return rc;
 }
 
+// One sync segment of an epoch: queued, not synchronised; the kernel adds its loss to c->loss_sum (the caller zeroes it
+// once per epoch and reads it once at the end).
+int queue_train(Ctx *c, uint64_t begin, uint64_t end)
+{
+    if (int rc = check_range(c, begin, end)) return rc;
+    if (begin == end) return 0;
+    HEAT_CUDA(cudaMemsetAsync(c->chunk_counter, 0, sizeof(unsigned long long), c->stream));
+    const TrainParams P = make_params(c, begin, end, c->chunk_counter, c->loss_sum, nullptr);
+    return run_engine(c, P);
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // heat_train_range_noalloc -- heat_train_range for callers that may not allocate (include/heat_b200.h).  Everything the
@@ -227,13 +261,10 @@ int noalloc_scratch(int device, unsigned char **out)
 
 int launch_train_noalloc(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, float *loss_per_sample_host)
 {
-    if (!c->clicks) return fail("heat_set_dataset has not been called");
-    if (!c->user_w) return fail("heat_bind_tables has not been called");
-    if (end > c->n_samples || begin > end) return fail("sample range out of bounds");
+    if (int rc = check_range(c, begin, end)) return rc;
     if (end - begin > (uint64_t)HEAT_NOALLOC_MAX_SAMPLES)
         return fail("heat_train_range_noalloc: " + std::to_string(end - begin) + " samples exceed HEAT_NOALLOC_MAX_SAMPLES (" +
                     std::to_string((uint64_t)HEAT_NOALLOC_MAX_SAMPLES) + "), the size of the library's static scratch; split the range");
-    if (c->max_his > 128) return fail("max_his > 128 is not supported by the training kernel");
     if (loss_sum_host) *loss_sum_host = 0.0;
     if (begin == end) { c->last_kernel_ms = 0.f; return 0; }
 
@@ -246,34 +277,8 @@ int launch_train_noalloc(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_
     // written by the kernel before they are read back)
     HEAT_CUDA(cudaMemsetAsync(scratch, 0, 16, c->stream));
 
-    TrainParams P{};
-    P.clicks = c->clicks; P.his = c->his; P.masks = c->masks;
-    P.user_w = c->user_w; P.item_w = c->item_w; P.user_g = c->user_g; P.item_g = c->item_g; P.w0 = c->w0;
-    P.chunk_counter = counter; P.loss_sum = loss_sum; P.loss_out = loss_out;
-    P.begin = (long long)begin; P.end = (long long)end;
-    P.sample_offset = c->cfg.sample_offset; P.seed = c->cfg.seed;
-    set_sampler(c, P);
-    P.epoch = (unsigned)c->epoch;
-    P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
-    P.chunk = (int)c->cfg.chunk;
-    P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
-    P.upd = (int)c->cfg.update_mode;
-    P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
-    P.no_cache = c->cfg.history_mode == 1;
-
-    // same engine choice as launch_train
-    int rc = -1;
-    c->last_engine = 0;
-    const int auto_w = c->cfg.engine == 0 ? auto_warp_engine(c, (int)c->cfg.emb_dim, P.K) : 0;
-    if (auto_w) { rc = dispatch(c, P, false, auto_w); c->last_engine = 1; }
-    else if (c->cfg.engine != 1 && c->cfg.engine != 3) { rc = dispatch_cta(c, P, c->cfg.deterministic != 0); c->last_engine = 2; }
-    if (rc == -1 && c->cfg.engine == 2) rc = fail("engine 2 (CTA per sample) does not cover this (emb_dim, num_negs)");
-    if (rc == -1) {
-        const bool det = c->cfg.deterministic != 0;
-        if (c->cfg.engine == 3 || (c->cfg.engine == 0 && !warp_covers((int)c->cfg.emb_dim, P.K))) { rc = dispatch_bigk(c, P, det); c->last_engine = 3; }
-        else { rc = dispatch(c, P, det); c->last_engine = 1; }
-    }
-    if (rc) return rc;
+    const TrainParams P = make_params(c, begin, end, counter, loss_sum, loss_out);
+    if (int rc = run_engine(c, P)) return rc;
     double loss = 0.0;
     cudaError_t e = cudaMemcpyAsync(&loss, loss_sum, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess && loss_per_sample_host)

@@ -168,9 +168,12 @@ def build_history(train_indptr, train_items, max_his: int, seed: int):
     return his, masks
 
 
-def generate_named(name: str, max_his: int = 100, seed: int = 2022) -> ClickData:
+def generate_named(name: str, max_his: int = 100, seed: int = 2022, users_mult: int = 1) -> ClickData:
+    """`users_mult` > 1 is the weak-scaling form of a shape: users_mult x the users and interactions over the SAME item
+    catalogue (one seed, so one item-cluster map and one popularity law), to be split by user range across that many
+    ranks (heat_b200/shard.py)."""
     u, i, n = SHAPES[name]
-    return generate(u, i, n, max_his=max_his, seed=seed)
+    return generate(u * users_mult, i, n * users_mult, max_his=max_his, seed=seed)
 
 
 def init_tables(num_users: int, num_items: int, emb_dim: int, seed: int = 2022):

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define HEAT_ABI_VERSION 1
+#define HEAT_ABI_VERSION 2
 
 typedef struct heat_ctx heat_ctx;
 
@@ -79,6 +79,12 @@ typedef struct heat_config {
                                    Alg. 1): the samples of one window of refresh_interval samples draw their negatives
                                    from a Philox-defined tile of tile_size item ids (philox.cuh).  0 (default): as the
                                    reference's shipped loop, the tile is ignored */
+    uint32_t sync_grads;        /* multi-GPU: 1 = the persistent item grad rows are reconciled together with the item table
+                                   (g = clamp(g_base + sum of rank deltas)), so that every rank steps with the running sum of
+                                   ALL ranks' touches, as one GPU training the union of the shards would; 0 = grad rows stay
+                                   local to a rank.  Only matters with more than one exchange per epoch (the rows are zeroed
+                                   at every epoch end) */
+    uint32_t reserved0;
 } heat_config;
 
 /* ---- life cycle -------------------------------------------------------------------- */
@@ -208,6 +214,20 @@ int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[1
  * the W0 delta since the last sync; every rank ends with base + sum of deltas. */
 int heat_comm_sync_items(heat_ctx *ctx);
 int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);   /* 0 = once per epoch */
+/* exchanges of the last heat_train_epoch and their total device time (CUDA events on the context's stream), ms */
+int heat_last_exchange(heat_ctx *ctx, uint64_t *count, float *ms);
+/* Multi-rank emulation on ONE device, for convergence tests and interval studies on a single-GPU box: n contexts
+ * created on the same device, context r holding rank r's user shard and its own replica of the item table and W0, train
+ * one epoch exactly as n ranks would -- every rank's segment, then the reconciliation of heat_comm_sync_items (same
+ * arithmetic, same rank order, same sync_average / sync_grads / sync interval, taken from ctxs[0]) -- only one rank after
+ * the other instead of side by side.  heat_local_group_init snapshots the base copies (call it after heat_bind_tables).
+ * *mean_loss = sum of all ranks' losses / all ranks' samples (what rank 0 of a real run returns). */
+int heat_local_group_init(heat_ctx **ctxs, int n);
+int heat_local_group_train_epoch(heat_ctx **ctxs, int n, double *mean_loss);
+/* Experiment knob of the emulation group (what would a finer-grained exchange buy?): the members SHARE one physical
+ * array instead of reconciling copies -- mask bit 0: W0, bit 1: the item grad rows, bit 2: the item table.  Call once,
+ * right after heat_local_group_init. */
+int heat_local_group_share(heat_ctx **ctxs, int n, uint32_t mask);
 /* how heat_comm_sync_items exchanges: 0 no communicator, 1 NCCL all-reduce, 2 fused peer-memory kernel */
 int heat_comm_mode(heat_ctx *ctx, int *mode);
 /* replaces: MPI_Allreduce of loss / iteration count (engine.cpp:380-383) for caller-side sums, e.g. the
@@ -218,6 +238,9 @@ int heat_comm_allreduce_f64(heat_ctx *ctx, double *vals, int n);
 /* L2-resident row gather/scatter micro-benchmark used as the L2 roofline denominator:
  * random 256-byte rows of a `bytes`-sized buffer are read and rewritten. GB/s (read+write). */
 int heat_probe_l2_bandwidth(int device, uint64_t bytes, int iters, double *gbps);
+/* Dense TF32 tensor peak of this GPU, measured: nothing but back-to-back tcgen05.mma.kind::tf32 (M128 N256 K8, operands in
+ * shared memory, accumulators in TMEM) on every SM; the roofline denominator of the evaluation kernel. TFLOP/s. */
+int heat_probe_tf32_peak(int device, int iters, double *tflops);
 /* page-locked host memory for the end-to-end path */
 int heat_host_alloc(void **ptr, uint64_t bytes);
 int heat_host_free(void *ptr);

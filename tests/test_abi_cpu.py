@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     L = abi.lib()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.heat_abi_version() == 1
+    assert L.heat_abi_version() == 2
 
 
 def test_host_sampler_twin_matches_oracle():
