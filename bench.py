@@ -6,15 +6,19 @@ A "step" is one training epoch (Engine::train_one_epoch) over the workload's syn
 LR schedule, every sample through the fused sampler+forward+backward+SGD kernel, zero_grad.  At N=1
 the workload is BASELINE.json configs[2], the configuration the metric is quoted on: Amazon-Books
 shape (52 643 users, 91 599 items, 2 380 730 interactions), dim 64, 16 negatives, max_his 100.  At
-N>1 every rank owns one such user shard (users split by id range, weak scaling), the item table and
-W0 are replicated and their deltas all-reduced over NCCL every `sync_interval` samples.
+N>1 ONE dataset of N x those users over the same item catalogue (one seed: one item-cluster map and
+popularity law) is split by contiguous user range (heat_b200/shard.py; cf_cpu/cf/main.py:51-66), rank r
+trains shard r (weak scaling), the item table and W0 are replicated and reconciled over NVLink every
+`sync_interval` samples (heat_comm_sync_items).  Other workloads (`--workload yelp18|gowalla|cfg4|cfg5-shard`)
+time the other BASELINE.json configs on one GPU.
 
 One JSON line on stdout (rank 0).  `value` = samples/s with everything resident in HBM (device time,
 CUDA events on the library's stream, max over ranks); `e2e` = the same epoch through the C ABI with
 HOST buffers (dataset + tables uploaded from pinned memory, trained, tables copied back) inside the
-timed region; `roofline` = the fused kernel's algorithmic bytes over its CUDA-event time against
-the measured HBM peak (and against the measured L2 row-gather peak, the bound that applies while
-the tables fit L2); `cpu_baseline` = the unmodified reference C++ (oracle/_ref) on the host cores.
+timed region; `roofline` = the fused kernel's algorithmic bytes over its CUDA-event time against the
+bound that applies -- the measured L2 row gather/scatter peak while weights + grads fit L2, the measured
+HBM copy peak otherwise; `cpu_baseline` = the unmodified reference C++ (oracle/_ref) on the host cores;
+at N>1 `convergence` = Recall@20 of a fresh N-rank run against ONE GPU training the same union dataset.
 """
 from __future__ import annotations
 
@@ -31,19 +35,32 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-D, K, MAX_HIS = 64, 16, 100
+MAX_HIS = 100
 METRIC, UNIT = "train_samples_per_sec", "samples/s"
+L2_BYTES = 126 << 20
+
+# name -> shape of heat_b200.synth, emb_dim, num_negs, clip_val of the shape's YAML, index in BASELINE.json configs
+WORKLOADS = {
+    "amazon-book": dict(shape="amazon-book", D=64, K=16, clip=1.0, cfg=2),
+    "yelp18": dict(shape="yelp18", D=64, K=16, clip=1.0, cfg=1),
+    "gowalla": dict(shape="gowalla", D=64, K=16, clip=0.1, cfg=0),
+    "cfg4": dict(shape="amazon-book", D=128, K=1000, clip=1.0, cfg=3),
+    # one GPU's shard of configs[4] (10 M users x 2 M items x 500 M interactions on 8 GPUs)
+    "cfg5-shard": dict(shape=None, users=1_250_000, items=2_000_000, samples=62_500_000, D=64, K=16, clip=1.0, cfg=4),
+}
+# library defaults of the multi-GPU exchange (heat_b200/cf/main.py uses the same): see DESIGN.md section 7
+DEFAULT_SYNC = dict(interval=0, average=0, grads=0)       # 0 = the library defaults: auto interval, mean of the replicas
 
 
-def algorithmic_bytes(clicks, masks, d=D, k=K):
+def algorithmic_bytes(clicks, masks, d=64, k=16):
     """B(D,K,H) = 4D(4(2+K)+H) + 12 + 4H per sample, H = masks[user]."""
     h = masks[clicks[:, 0].astype(np.int64), 0].astype(np.float64)
     return float(np.sum(4 * d * (4 * (2 + k) + h) + 12 + 4 * h))
 
 
 def ncu_traffic(kernel_file):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed ncu --set full capture."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", kernel_file)
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch from a committed ncu --set full capture."""
+    path = os.path.join(ROOT, "profiles", kernel_file)
     try:
         import csv
         with open(path) as f:
@@ -115,64 +132,92 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def make_workload(name, rank=0):
-    """Seeded synthetic click data of the named shape; rank r gets its own user shard (seed 2022+r)."""
-    from heat_b200 import synth
-    d = synth.generate_named(name, max_his=MAX_HIS, seed=2022 + rank)
-    tables = synth.init_tables(d.num_users, d.num_items, D, seed=2022)   # item table / W0 replicated
-    if rank:
-        tables = (synth.init_tables(d.num_users, d.num_items, D, seed=2022 + rank)[0], tables[1], tables[2])
-    return d, tables
+def make_workload(name, rank=0, world=1, want_union=False):
+    """Seeded synthetic click data of the named workload.  world > 1: ONE dataset with world x the users of the shape
+    over the same items (seed 2022), of which rank r gets user range r.  Returns (local ClickData, local tables,
+    global index of the local sample 0, union ClickData or None, union tables or None)."""
+    from heat_b200 import shard, synth
+    w = WORKLOADS[name]
+    if w["shape"] is None:
+        if world > 1:
+            raise SystemExit("cfg5-shard is one GPU's shard; the 8-GPU run of BASELINE configs[4] is tools/bench_scale.py under torchrun")
+        d = synth.generate_powerlaw(w["users"], w["items"], w["samples"], seed=2022)
+        return d, synth.init_tables(d.num_users, d.num_items, w["D"], seed=2022), 0, None, None
+    union = synth.generate_named(w["shape"], max_his=MAX_HIS, seed=2022, users_mult=world)
+    ut = synth.init_tables(union.num_users, union.num_items, w["D"], seed=2022)
+    if world == 1:
+        return union, ut, 0, None, None
+    local, off = shard.shard_clicks(union, rank, world)
+    u0, u1 = shard.user_range(union.num_users, rank, world)
+    tables = (np.ascontiguousarray(ut[0][u0:u1]), ut[1], ut[2])          # item table / W0 replicated, user rows sharded
+    return local, tables, off, (union if want_union else None), (ut if want_union else None)
 
 
-def cpu_reference_run(d, tables, n_samples, epochs, threads=0):
-    """The reference's own C++ per-sample code (oracle/_ref, compiled unmodified from
-    /root/reference) -- or the C restatement when that library is absent -- over the first
-    n_samples samples, upstream OpenMP loop, all host threads.  Returns (seconds per epoch list,
-    kind, threads, mean loss)."""
+def cpu_reference_run(w, d, tables, n_samples, epochs, threads, opt="O3"):
+    """The reference's own C++ per-sample code (oracle/_ref, compiled unmodified from /root/reference; opt "O0" = its
+    own flags, no -O) -- or the C restatement when that library is absent -- over the first n_samples samples, upstream
+    OpenMP loop.  Returns (seconds per epoch list, kind, threads, mean loss)."""
     import oracle
     clicks = np.ascontiguousarray(d.clicks[:n_samples])
     uw, iw, w0 = (t.copy() for t in tables)
-    if oracle.RefOracle.available():
-        o = oracle.RefOracle(D, K, clicks, d.his_items, d.masks, uw, iw, w0)
-        kind, nthr = "reference", o.max_threads()
+    if oracle.RefOracle.available(opt):
+        o = oracle.RefOracle(w["D"], w["K"], clicks, d.his_items, d.masks, uw, iw, w0, clip_val=w["clip"], opt=opt)
+        kind = "reference"
         run = lambda: o.train_epoch(nthreads=threads, sampler=0)          # its own mt19937 sampler
     else:
-        o = oracle.COracle(D, K, clicks, d.his_items, d.masks, uw, iw, w0)
-        kind, nthr = "port", os.cpu_count() or 1
+        o = oracle.COracle(w["D"], w["K"], clicks, d.his_items, d.masks, uw, iw, w0, clip_val=w["clip"])
+        kind = "port"
         run = lambda: o.train_epoch(nthreads=threads)
-    if threads:
-        nthr = threads
     secs, loss = [], 0.0
     for _ in range(epochs):
         t0 = time.perf_counter()
         loss = run()
         secs.append(time.perf_counter() - t0)
     o.close()
-    return secs, kind, nthr, loss
+    return secs, kind, threads, loss
 
 
-def cpu_baseline(d, tables, budget_s=12.0):
-    """Bounded sample: calibrate on 100k samples, then one pass sized for ~budget_s of CPU work."""
-    n0 = min(100_000, d.train_size)
-    s0, kind, nthr, _ = cpu_reference_run(d, tables, n0, 1)
+def host_threads():
+    """All host cores, stated explicitly: torch.distributed.run exports OMP_NUM_THREADS=1, which would otherwise turn the
+    reference arm into a single-thread run."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_baseline(w, d, tables, budget_s=12.0):
+    """Bounded sample: calibrate on 100k samples, then one pass sized for ~budget_s of CPU work; the reference's own
+    build flags (no -O, CMakeLists.txt:5-17: build A of BASELINE.md section 2) timed beside the -O3 build (B)."""
+    import oracle
+    thr = host_threads()
+    n0 = min(100_000 if w["K"] <= 64 else 2_000, d.train_size)
+    s0, kind, nthr, _ = cpu_reference_run(w, d, tables, n0, 1, thr)
     rate = n0 / s0[0]
     n = int(min(d.train_size, max(n0, rate * budget_s)))
-    secs, kind, nthr, loss = cpu_reference_run(d, tables, n, 1)
-    return {"value": n / secs[0], "unit": UNIT, "cores": nthr, "kind": kind,
-            "sample": f"first {n} of {d.train_size} samples, 1 pass, {secs[0]:.2f} s, OpenMP schedule(dynamic,512)",
-            "loss": loss}
+    secs, kind, nthr, loss = cpu_reference_run(w, d, tables, n, 1, thr)
+    out = {"value": n / secs[0], "unit": UNIT, "cores": nthr, "kind": kind,
+           "sample": f"first {n} of {d.train_size} samples, 1 pass, {secs[0]:.2f} s, OpenMP schedule(dynamic,512), build B (-O3)",
+           "loss": loss}
+    if kind == "reference" and oracle.RefOracle.available("O0"):
+        nA = max(n0 // 4, int(min(n, rate * budget_s / 12)))               # the unoptimised build is ~10x slower
+        sA, _, _, _ = cpu_reference_run(w, d, tables, nA, 1, thr, opt="O0")
+        out["build_A_reference_flags"] = {"value": nA / sA[0], "unit": UNIT, "cores": nthr,
+                                          "sample": f"first {nA} samples, 1 pass, {sA[0]:.2f} s, the reference's own flags (no -O)"}
+    return out
 
 
 def run_reference_arm(args, rank, world):
     """--impl reference: the reference's CPU implementation of the path on this box's host cores."""
     if rank != 0:
         return
-    d, tables = make_workload(args.workload)
-    n0 = min(100_000, d.train_size)
-    s0, kind, nthr, _ = cpu_reference_run(d, tables, n0, 1)
+    w = WORKLOADS[args.workload]
+    d, tables, _, _, _ = make_workload(args.workload)
+    thr = host_threads()
+    n0 = min(100_000 if w["K"] <= 64 else 2_000, d.train_size)
+    s0, kind, nthr, _ = cpu_reference_run(w, d, tables, n0, 1, thr)
     n = int(min(d.train_size, max(n0, (n0 / s0[0]) * args.ref_step_seconds)))
-    secs, kind, nthr, loss = cpu_reference_run(d, tables, n, args.warmup + args.steps)
+    secs, kind, nthr, loss = cpu_reference_run(w, d, tables, n, args.warmup + args.steps, thr)
     timed = secs[args.warmup:]
     value = n * len(timed) / sum(timed)
     sample = f"each step = first {n} of {d.train_size} samples, upstream OpenMP loop, {nthr} threads"
@@ -187,11 +232,20 @@ def run_reference_arm(args, rank, world):
 
 
 def workload_config(args, d, world):
-    return {"workload": f"{args.workload}-shaped synthetic MF_CCL (BASELINE.json configs[2])",
+    w = WORKLOADS[args.workload]
+    table_mb = 2 * (d.num_users + d.num_items) * w["D"] * 4 / 1e6
+    return {"workload": f"{args.workload}: synthetic MF_CCL of BASELINE.json configs[{w['cfg']}]" +
+                        (f", {world} x the users over the same items, split by user range" if world > 1 else ""),
             "users_per_gpu": d.num_users, "items": d.num_items, "samples_per_gpu": d.train_size,
-            "emb_dim": D, "num_negs": K, "max_his": MAX_HIS, "optimizer": "sgd+clip (persistent grad rows)",
+            "emb_dim": w["D"], "num_negs": w["K"], "max_his": MAX_HIS, "optimizer": "sgd+clip (persistent grad rows)",
             "parallelism": f"user-sharded x{world}" if world > 1 else "single GPU",
-            "l2": "flushed between timed steps (256 MiB write); within a step the 74 MB of tables stay L2-resident by design"}
+            "l2": f"flushed between timed steps (256 MiB write); within a step the {table_mb:.0f} MB of weights + grads " +
+                  ("stay L2-resident by design" if table_mb * 1e6 < L2_BYTES else "exceed L2 (HBM-resident)")}
+
+
+def new_context(abi, w, d, args, off, local_rank, **kw):
+    return abi.Context(w["D"], w["K"], d.num_users, d.num_items, clip_val=w["clip"], l_r=1e-2, milestones=(10,), seed=2022,
+                       sample_offset=off, device=local_rank, sync_average=args.sync_average, sync_grads=args.sync_grads, **kw)
 
 
 def run_gpu_arm(args, rank, world, local_rank):
@@ -199,10 +253,13 @@ def run_gpu_arm(args, rank, world, local_rank):
     import torch.distributed as dist
     from heat_b200 import abi
 
+    w = WORKLOADS[args.workload]
+    D, K = w["D"], w["K"]
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    d, tables = make_workload(args.workload, rank)
+    want_conv = world > 1 and not args.no_convergence
+    d, tables, off, union, union_tables = make_workload(args.workload, rank, world, want_union=want_conv and rank == 0)
     N = d.train_size
 
     # pinned host copies: the buffers the reference frontend would own (uint64 ids, fp32 tables)
@@ -214,18 +271,20 @@ def run_gpu_arm(args, rank, world, local_rank):
     uw, iw, w0 = (pin(t) for t in tables)
     init = [t.copy() for t in tables]
 
-    ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=1.0, l_r=1e-2, milestones=(10,), seed=2022,
-                      sample_offset=rank * N, device=local_rank, update_mode=args.update_mode,
-                      warps_per_block=args.warps, max_blocks=args.max_blocks, chunk=args.chunk, engine=args.engine)
+    def connect(ctx):
+        if world > 1:
+            uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                uid.copy_(torch.from_numpy(abi.Context.comm_unique_id()))
+            dist.broadcast(uid, 0)
+            ctx.comm_init(rank, world, uid.cpu().numpy())
+            ctx.set_sync_interval(args.sync_interval)
+
+    ctx = new_context(abi, w, d, args, off, local_rank, update_mode=args.update_mode, warps_per_block=args.warps,
+                      max_blocks=args.max_blocks, chunk=args.chunk, engine=args.engine)
     ctx.set_dataset(clicks, his, masks)
     ctx.bind_tables(uw, iw, w0)
-    if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            uid.copy_(torch.from_numpy(abi.Context.comm_unique_id()))
-        dist.broadcast(uid, 0)
-        ctx.comm_init(rank, world, uid.cpu().numpy())
-        ctx.set_sync_interval(args.sync_interval)
+    connect(ctx)
     exchange = {0: None, 1: "NCCL all-reduce of the item/W0 delta", 2: "fused peer-memory exchange kernel (CUDA IPC over NVLink)"}[ctx.comm_mode()]
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -240,12 +299,14 @@ def run_gpu_arm(args, rank, world, local_rank):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def reduce_max(x):
+    def reduce(x, op="max"):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
         return float(t.item())
+
+    n_total = int(reduce(float(N), "sum"))
 
     # ---- resident arm: tables and dataset stay in HBM; a step = heat_train_epoch
     losses = []
@@ -253,18 +314,20 @@ def run_gpu_arm(args, rank, world, local_rank):
         flush_l2(); losses.append(ctx.train_epoch())
     launches0 = ctx.launch_count()
     barrier()
-    epoch_ms, kernel_ms = [], []
+    epoch_ms, kernel_ms, xch_ms, xch_n = [], [], [], 0
     wall0 = time.perf_counter()
     with ClockSampler(local_rank) as clk:
         for _ in range(args.steps):
             flush_l2()
             losses.append(ctx.train_epoch())
             epoch_ms.append(ctx.last_epoch_ms()); kernel_ms.append(ctx.last_kernel_ms())
+            xch_n, x = ctx.last_exchange(); xch_ms.append(x)
         barrier()
     wall = time.perf_counter() - wall0
     launches = ctx.launch_count() - launches0
-    total_ms = reduce_max(float(np.sum(epoch_ms)))
-    value = world * N * args.steps / (total_ms * 1e-3)
+    total_ms = reduce(float(np.sum(epoch_ms)))
+    value = n_total * args.steps / (total_ms * 1e-3)
+    engine_ran = ctx.last_engine()
 
     # ---- end-to-end arm: host buffers in, trained host tables out, every step
     h2d = clicks.nbytes + his.nbytes + masks.nbytes + uw.nbytes + iw.nbytes + w0.nbytes
@@ -285,8 +348,8 @@ def run_gpu_arm(args, rank, world, local_rank):
         flush_l2()
         e2e_step()
     barrier()
-    e2e_s = reduce_max(time.perf_counter() - t0)
-    e2e_value = world * N * e2e_steps / e2e_s
+    e2e_s = reduce(time.perf_counter() - t0)
+    e2e_value = n_total * e2e_steps / e2e_s
 
     # ---- evaluation leg ("eval ms" of BASELINE.json's metric): U.I^T on tcgen05 (3xTF32) fused with the masked top-50
     #      and Recall/NDCG/HitRate, on the tables the epochs above trained; every rank evaluates its own user shard.
@@ -297,16 +360,23 @@ def run_gpu_arm(args, rank, world, local_rank):
         for i in range(2 + 5):
             flush_l2()
             t0 = time.perf_counter()
-            res, _ = ctx.eval_metrics(d.train_indptr, d.train_items, d.test_indptr, d.test_items)
+            res, sums = ctx.eval_metrics(d.train_indptr, d.train_items, d.test_indptr, d.test_items)
             if i >= 2:
                 ev_wall.append((time.perf_counter() - t0) * 1e3); ev_ms.append(ctx.last_eval_ms())
-        ev_ms_max = reduce_max(float(np.mean(ev_ms)))
+        ev_ms_max = reduce(float(np.mean(ev_ms)))
+        if world > 1:                                # user-sharded evaluation: the seven metric sums all-reduced
+            s = ctx.allreduce_f64(sums)
+            res = dict(zip(res.keys(), (s[:6] / max(s[6], 1.0)).tolist()))
         flops = 2.0 * d.num_users * d.num_items * D
-        tf32_peak = 1125.0                                   # TFLOP/s dense, nominal (half the bf16 rate; no measured TF32 peak on file)
+        tf32_peak, tf32_src = 1125.0, "nominal dense TF32"
+        try:
+            tf32_peak, tf32_src = abi.probe_tf32_peak(local_rank), "measured: heat_probe_tf32_peak (bare tcgen05.mma.kind::tf32 loop on every SM)"
+        except abi.HeatError as e:
+            tf32_src = f"nominal dense TF32 (probe failed: {e})"
         ev = {"ms": ev_ms_max, "wall_ms_with_csr_upload": float(np.mean(ev_wall)), "users_per_gpu": int(d.num_users),
               "items": int(d.num_items), "k": 50, "metrics": res,
               "roofline": {"bound": "tensor", "achieved": 3 * flops / (ev_ms_max * 1e-3) / 1e12, "peak": tf32_peak, "unit": "TFLOP/s",
-                           "frac": 3 * flops / (ev_ms_max * 1e-3) / 1e12 / tf32_peak,
+                           "frac": 3 * flops / (ev_ms_max * 1e-3) / 1e12 / tf32_peak, "peak_source": tf32_src,
                            "note": "executed TF32 flops (3 passes of 2*U*I*D: A_lo.B_hi + A_hi.B_lo + A_hi.B_hi); fp32-equivalent "
                                    "work is a third of it; includes the TF32 split of both tables and the metrics kernel",
                            "fp32_equivalent_tflops": flops / (ev_ms_max * 1e-3) / 1e12}}
@@ -316,20 +386,12 @@ def run_gpu_arm(args, rank, world, local_rank):
     #      samples in flight).  Faster, but its Hogwild dynamics leave the reference's Recall@20,
     #      so it is not the configuration `value` is quoted on.
     thr = None
-    if args.engine == 0 and not args.no_throughput_mode:
+    if args.engine == 0 and engine_ran == 2 and world == 1 and not args.no_throughput_mode:
         for t, t0_ in zip((uw, iw, w0), init):
             t[...] = t0_
-        ctx2 = abi.Context(D, K, d.num_users, d.num_items, clip_val=1.0, l_r=1e-2, milestones=(10,), seed=2022,
-                           sample_offset=rank * N, device=local_rank, engine=1)
+        ctx2 = new_context(abi, w, d, args, off, local_rank, engine=1)
         ctx2.set_dataset(clicks, his, masks)
         ctx2.bind_tables(uw, iw, w0)
-        if world > 1:
-            uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
-            if rank == 0:
-                uid.copy_(torch.from_numpy(abi.Context.comm_unique_id()))
-            dist.broadcast(uid, 0)
-            ctx2.comm_init(rank, world, uid.cpu().numpy())
-            ctx2.set_sync_interval(args.sync_interval)
         for _ in range(args.warmup):
             flush_l2(); ctx2.train_epoch()
         barrier()
@@ -338,11 +400,43 @@ def run_gpu_arm(args, rank, world, local_rank):
             flush_l2(); ctx2.train_epoch()
             ms2.append(ctx2.last_epoch_ms()); k2.append(ctx2.last_kernel_ms())
         barrier()
-        tot2 = reduce_max(float(np.sum(ms2)))
-        thr = {"value": world * N * args.steps / (tot2 * 1e-3), "unit": UNIT, "ms_per_step": tot2 / args.steps,
+        tot2 = float(np.sum(ms2))
+        thr = {"value": N * args.steps / (tot2 * 1e-3), "unit": UNIT, "ms_per_step": tot2 / args.steps,
                "kernel": "heat::train_kernel (warp per sample, full grid)", "kernel_ms": float(np.mean(k2)),
-               "recall_parity": "outside the 0.005 tolerance (profiles/r01_recall_parity.md)"}
+               "recall_parity": "outside the 0.005 tolerance (DESIGN.md section 6)"}
         ctx2.close()
+
+    # ---- convergence at N > 1: a fresh N-rank run with this exchange policy against ONE GPU training the same union
+    #      dataset (what --gpus 1 would do with this data), Recall@20 over all users.
+    conv = None
+    if want_conv:
+        E = args.convergence_epochs or (args.warmup + args.steps)
+        for t, t0_ in zip((uw, iw, w0), init):
+            t[...] = t0_
+        c3 = new_context(abi, w, d, args, off, local_rank, engine=args.engine, max_blocks=args.max_blocks)
+        c3.set_dataset(clicks, his, masks)
+        c3.bind_tables(uw, iw, w0)
+        connect(c3)
+        closs = [c3.train_epoch() for _ in range(E)]
+        _, sums = c3.eval_metrics(d.train_indptr, d.train_items, d.test_indptr, d.test_items)
+        s = c3.allreduce_f64(sums)
+        c3.close()
+        conv = {"epochs": E, "losses": closs, "recall_at_20": float(s[0] / s[6]), "recall_at_50": float(s[1] / s[6])}
+        if rank == 0:
+            t1 = [t.copy() for t in union_tables]
+            c4 = abi.Context(D, K, union.num_users, union.num_items, clip_val=w["clip"], l_r=1e-2, milestones=(10,), seed=2022,
+                             device=local_rank, engine=args.engine, max_blocks=args.max_blocks)
+            c4.set_dataset(union.clicks, union.his_items, union.masks)
+            c4.bind_tables(*t1)
+            l1 = [c4.train_epoch() for _ in range(E)]
+            r1, _ = c4.eval_metrics(union.train_indptr, union.train_items, union.test_indptr, union.test_items)
+            ms1 = c4.last_epoch_ms()
+            c4.close()
+            conv.update({"n1_same_data": {"losses": l1, "recall_at_20": r1["Recall(k=20)"], "recall_at_50": r1["Recall(k=50)"],
+                                          "ms_per_epoch": ms1, "what": "one GPU, library defaults, the union of all shards"},
+                         "recall_vs_n1": conv["recall_at_20"] - r1["Recall(k=20)"],
+                         "max_abs_loss_vs_n1": float(np.max(np.abs(np.array(closs) - np.array(l1))))})
+        barrier()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -350,21 +444,32 @@ def run_gpu_arm(args, rank, world, local_rank):
         return
 
     # ---- roofline of the fused training kernel (dominant: one launch per epoch at N=1)
-    alg = algorithmic_bytes(d.clicks, d.masks)
+    alg = algorithmic_bytes(d.clicks, d.masks, D, K)
     k_ms = float(np.mean(kernel_ms))
-    peak, peak_src = measured_peaks()
+    hbm_peak, hbm_src = measured_peaks()
     achieved = alg / (k_ms * 1e-3) / 1e9
     table_bytes = 2 * (d.num_users + d.num_items) * D * 4
-    l2_peak = abi.probe_l2_bandwidth(local_rank, table_bytes, 200)
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": args.ncu_traffic if args.ncu_traffic is not None else ncu_traffic(
-                    "r01_train_cta_kernel_ncu_raw.csv" if args.engine != 1 else "r01_train_kernel_ncu_raw.csv"),
-                "traffic_source": "profiles/ ncu --set full capture of the same bench command (bytes per launch)", "peak_source": peak_src,
-                "kernel": "heat::train_cta_kernel" if args.engine != 1 else "heat::train_kernel",
-                "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
-                "note": "weights+grads (%.0f MB) are L2-resident: the bound that applies is the L2 row "
-                        "gather/scatter rate, measured by heat_probe_l2_bandwidth on the same footprint" % (table_bytes / 1e6),
-                "l2_peak": l2_peak, "l2_frac": achieved / l2_peak}
+    kernel = {1: "heat::train_kernel", 2: "heat::train_cta_kernel", 3: "heat::train_bigk_kernel"}.get(engine_ran, "?")
+    cap = {2: "r01_train_cta_kernel_ncu_raw.csv", 1: "r01_train_kernel_ncu_raw.csv", 3: "r01_bigk_kernel_ncu_raw.csv"}.get(engine_ran)
+    traffic = args.ncu_traffic if args.ncu_traffic is not None else (ncu_traffic(cap) if cap and args.workload in ("amazon-book", "cfg4") else None)
+    roofline = {"kernel": kernel, "kernel_ms": k_ms, "launches_per_step": max(1, int(xch_n)) if world > 1 else 1,
+                "algorithmic_bytes_per_step": alg, "achieved": achieved, "unit": "GB/s",
+                "traffic": traffic,
+                "traffic_source": None if traffic is None else f"profiles/{cap}: dram bytes of one launch in an EARLIER ncu --set full capture "
+                                                                "of this command (not re-measured in this run)",
+                "hbm_peak": hbm_peak, "hbm_peak_source": hbm_src, "hbm_frac": achieved / hbm_peak}
+    if table_bytes < L2_BYTES and engine_ran != 3:
+        l2_peak = abi.probe_l2_bandwidth(local_rank, table_bytes, 200)
+        roofline.update({"bound": "l2", "peak": l2_peak, "frac": achieved / l2_peak,
+                         "peak_source": "measured in this run: heat_probe_l2_bandwidth (random 256-byte row gather/scatter over the same "
+                                        "footprint, the access pattern of the kernel)",
+                         "note": "weights + grads (%.0f MB) are L2-resident (DRAM traffic is a fraction of a percent of the algorithmic "
+                                 "bytes), so the bound that applies is the L2 row gather/scatter rate (SURVEY.md 8.4); the HBM figures are "
+                                 "kept as hbm_peak / hbm_frac" % (table_bytes / 1e6)})
+    else:
+        roofline.update({"bound": "hbm", "peak": hbm_peak, "frac": achieved / hbm_peak, "peak_source": hbm_src,
+                         "note": "weights + grads (%.0f MB) exceed L2: HBM copy peak; rows re-used out of L2 let the algorithmic rate "
+                                 "pass the DRAM rate (traffic, where captured, says by how much)" % (table_bytes / 1e6)})
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -374,17 +479,24 @@ def run_gpu_arm(args, rank, world, local_rank):
                     "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "what": "heat_set_dataset + heat_upload_tables + heat_train_epoch + heat_sync_to_host from pinned host buffers"},
             "roofline": roofline, "loss_first_last": [losses[0], losses[-1]], "wall_s_timed_region": wall,
-            "update_mode": args.update_mode, "sync_interval": args.sync_interval if world > 1 else None, "exchange": exchange,
-            "engine": {0: "auto: CTA-per-sample kernel, parity-grade concurrency", 1: "warp-per-sample kernel, full grid",
-                       2: "CTA-per-sample kernel"}[args.engine]}
+            "update_mode": args.update_mode,
+            "engine": {1: "warp-per-sample kernel", 2: "CTA-per-sample kernel", 3: "large-negative kernel"}.get(engine_ran, "?") +
+                      (" (engine 0 = auto)" if args.engine == 0 else " (forced)")}
+    if world > 1:
+        line.update({"sync_interval": args.sync_interval, "sync_average": args.sync_average, "sync_grads": args.sync_grads,
+                     "exchange": exchange, "exchanges_per_epoch": int(xch_n), "exchange_ms_total": float(np.mean(xch_ms)),
+                     "exchange_share_of_epoch": float(np.mean(xch_ms)) / (total_ms / args.steps)})
     if ev is not None:
         line["eval"] = ev
+        line["recall_at_20"] = ev["metrics"]["Recall(k=20)"]
+    if conv is not None:
+        line["convergence"] = conv
+        line["recall_vs_n1"] = conv.get("recall_vs_n1")
     if thr is not None:
-        thr["l2_frac"] = alg / (thr["kernel_ms"] * 1e-3) / 1e9 / l2_peak
+        thr["l2_frac"] = alg / (thr["kernel_ms"] * 1e-3) / 1e9 / roofline["peak"] if roofline["bound"] == "l2" else None
         line["throughput_mode"] = thr
     if not args.no_cpu_baseline:
-        d0, t0_ = (d, init)
-        line["cpu_baseline"] = cpu_baseline(d0, t0_, args.cpu_seconds)
+        line["cpu_baseline"] = cpu_baseline(w, d, init, args.cpu_seconds)
     print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
@@ -397,14 +509,18 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="amazon-book")
+    ap.add_argument("--workload", default="amazon-book", choices=sorted(WORKLOADS))
     ap.add_argument("--update-mode", type=int, default=0)
     ap.add_argument("--warps", type=int, default=0)
     ap.add_argument("--max-blocks", type=int, default=0)
     ap.add_argument("--chunk", type=int, default=0)
-    ap.add_argument("--engine", type=int, default=0, help="0 auto (CTA-per-sample kernel at parity-grade concurrency), 1 warp-per-sample, 2 CTA-per-sample")
+    ap.add_argument("--engine", type=int, default=0, help="0 auto, 1 warp-per-sample, 2 CTA-per-sample, 3 large-negative")
     ap.add_argument("--no-throughput-mode", action="store_true", help="skip the extra warp-per-sample full-grid measurement")
-    ap.add_argument("--sync-interval", type=int, default=0, help="samples per GPU between item-delta all-reduces (0 = per epoch)")
+    ap.add_argument("--sync-interval", type=int, default=DEFAULT_SYNC["interval"], help="samples per GPU between exchanges of the replicated item table (0 = auto: max(65536, 3 x items))")
+    ap.add_argument("--sync-average", type=int, default=DEFAULT_SYNC["average"], help="0/1 mean of the replicas (the fork's averaging; default), 2 sum of the rank deltas")
+    ap.add_argument("--sync-grads", type=int, default=DEFAULT_SYNC["grads"], help="1 = the persistent item grad rows are exchanged too")
+    ap.add_argument("--no-convergence", action="store_true", help="N > 1: skip the Recall@20-vs-one-GPU leg")
+    ap.add_argument("--convergence-epochs", type=int, default=0, help="0 = warmup + steps, the epochs the timed tables saw")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eval", action="store_true", help="skip the evaluation leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)

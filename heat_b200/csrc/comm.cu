@@ -95,6 +95,17 @@ __global__ void apply_kernel(float4 *__restrict__ w, float4 *__restrict__ base, 
     }
 }
 
+// w = scale * sum (mean mode), clamped to +-clip when clip > 0
+__global__ void scale_kernel(float4 *__restrict__ w, const float4 *__restrict__ sum, float scale, float clip, size_t n4)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 d = sum[i];
+        float4 b = make_float4(d.x * scale, d.y * scale, d.z * scale, d.w * scale);
+        if (clip > 0.f) { b.x = clampc(b.x, clip); b.y = clampc(b.y, clip); b.z = clampc(b.z, clip); b.w = clampc(b.w, clip); }
+        w[i] = b;
+    }
+}
+
 // ---- fused exchange over peer memory ------------------------------------------------------------------------
 constexpr int MAX_PEERS = 8;
 struct PeerSync {
@@ -107,6 +118,7 @@ struct PeerSync {
     unsigned long long *flags[MAX_PEERS];          // [2][8] arrival counters of every rank
     unsigned long long seq;                        // this exchange's number (1, 2, ...)
     float scale;
+    int mean;                                      // 1: new = scale * sum_q w_q (no base copies involved)
     size_t n4_items, n4_w0;
     unsigned *grid_sync;                           // [0] release flag of the start barrier, [1] blocks done
 };
@@ -151,21 +163,53 @@ __device__ __forceinline__ void peer_barrier(const PeerSync &S, int which)
     __syncthreads();
 }
 
+// One slice of one replicated array.  U float4 per thread and replica are in flight at a time (U x world 16-byte loads,
+// world-1 of them over NVLink): the loop is bound by the number of bytes in flight, not by instruction issue.
+//   sum  mode (scale 1):      new = base + sum_q (w_q - base)      -> every replica and every base copy
+//   mean mode (scale 1/world): new = (1/world) sum_q w_q            -> every replica; algebraically base + mean of the
+//                              deltas, so the base copies are neither read nor written (half the remote stores)
+template <int U>
 __device__ __forceinline__ void peer_reduce_range(const PeerSync &S, float4 *const *w, float4 *const *base, size_t n4, float clip)
 {
     const size_t per = (n4 + S.slices - 1) / S.slices;
     const size_t lo = per * S.slice, hi = lo + per < n4 ? lo + per : n4;
-    for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
-        const float4 b = base[S.rank][i];
-        float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int q = 0; q < S.world; ++q) {
-            const float4 a = ld_sys4(w[q] + i);
-            d.x += a.x - b.x; d.y += a.y - b.y; d.z += a.z - b.z; d.w += a.w - b.w;
+    const bool mean = S.mean != 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i0 = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < hi; i0 += stride * U) {
+        float4 a[U][MAX_PEERS], b[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = i0 + u * stride;
+            if (i < hi) {
+                if (!mean) b[u] = base[S.rank][i];
+#pragma unroll
+                for (int q = 0; q < MAX_PEERS; ++q)
+                    if (q < S.world) a[u][q] = ld_sys4(w[q] + i);
+            }
         }
-        float4 nb;
-        nb.x = fmaf(S.scale, d.x, b.x); nb.y = fmaf(S.scale, d.y, b.y); nb.z = fmaf(S.scale, d.z, b.z); nb.w = fmaf(S.scale, d.w, b.w);
-        if (clip > 0.f) { nb.x = clampc(nb.x, clip); nb.y = clampc(nb.y, clip); nb.z = clampc(nb.z, clip); nb.w = clampc(nb.w, clip); }
-        for (int q = 0; q < S.world; ++q) { st_sys4(w[q] + i, nb); st_sys4(base[q] + i, nb); }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t i = i0 + u * stride;
+            if (i >= hi) continue;
+            float4 nb;
+            if (mean) {
+                float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int q = 0; q < MAX_PEERS; ++q)
+                    if (q < S.world) { d.x += a[u][q].x; d.y += a[u][q].y; d.z += a[u][q].z; d.w += a[u][q].w; }
+                nb = make_float4(d.x * S.scale, d.y * S.scale, d.z * S.scale, d.w * S.scale);
+            } else {
+                float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int q = 0; q < MAX_PEERS; ++q)
+                    if (q < S.world) { d.x += a[u][q].x - b[u].x; d.y += a[u][q].y - b[u].y; d.z += a[u][q].z - b[u].z; d.w += a[u][q].w - b[u].w; }
+                nb = make_float4(b[u].x + d.x, b[u].y + d.y, b[u].z + d.z, b[u].w + d.w);
+            }
+            if (clip > 0.f) { nb.x = clampc(nb.x, clip); nb.y = clampc(nb.y, clip); nb.z = clampc(nb.z, clip); nb.w = clampc(nb.w, clip); }
+#pragma unroll
+            for (int q = 0; q < MAX_PEERS; ++q)
+                if (q < S.world) { st_sys4(w[q] + i, nb); if (!mean) st_sys4(base[q] + i, nb); }
+        }
     }
 }
 
@@ -173,9 +217,9 @@ __device__ __forceinline__ void peer_reduce_range(const PeerSync &S, float4 *con
 // reduces every row of every array; same arithmetic and rank order as peer_sync_kernel / the NCCL path.
 __global__ void __launch_bounds__(256) local_sync_kernel(const PeerSync S)
 {
-    if (S.w[0]) peer_reduce_range(S, S.w, S.base, S.n4_items, 0.f);
-    if (S.w0[0]) peer_reduce_range(S, S.w0, S.w0b, S.n4_w0, 0.f);
-    if (S.g[0]) peer_reduce_range(S, S.g, S.gb, S.n4_items, S.clip);
+    if (S.w[0]) peer_reduce_range<2>(S, S.w, S.base, S.n4_items, 0.f);
+    if (S.w0[0]) peer_reduce_range<1>(S, S.w0, S.w0b, S.n4_w0, 0.f);
+    if (S.g[0]) peer_reduce_range<2>(S, S.g, S.gb, S.n4_items, S.clip);
 }
 
 __global__ void __launch_bounds__(256) peer_sync_kernel(const PeerSync S)
@@ -189,9 +233,9 @@ __global__ void __launch_bounds__(256) peer_sync_kernel(const PeerSync S)
         if (threadIdx.x == 0) while (ld_acquire_gpu(S.grid_sync) != seq32) { }
         __syncthreads();
     }
-    peer_reduce_range(S, S.w, S.base, S.n4_items, 0.f);
-    peer_reduce_range(S, S.w0, S.w0b, S.n4_w0, 0.f);
-    if (S.g[0]) peer_reduce_range(S, S.g, S.gb, S.n4_items, S.clip);
+    peer_reduce_range<2>(S, S.w, S.base, S.n4_items, 0.f);
+    peer_reduce_range<1>(S, S.w0, S.w0b, S.n4_w0, 0.f);
+    if (S.g[0]) peer_reduce_range<2>(S, S.g, S.gb, S.n4_items, S.clip);
     // end barrier: my stores have landed in every replica and every peer's stores have landed in mine before any
     // later kernel of this stream starts; the last block to finish carries it
     __threadfence_system();
@@ -265,7 +309,8 @@ int peer_sync(Ctx *c)
     S.clip = c->cfg.clip_val;
     const size_t D = c->cfg.emb_dim;
     S.seq = c->syncs + 1;
-    S.scale = c->cfg.sync_average ? 1.0f / (float)c->world : 1.0f;
+    S.scale = sync_mean(c) ? 1.0f / (float)c->world : 1.0f;
+    S.mean = sync_mean(c) ? 1 : 0;
     S.n4_items = c->cfg.num_items * D / 4; S.n4_w0 = D * D / 4;
     S.grid_sync = c->grid_sync;
     peer_sync_kernel<<<c->num_sms, 256, 0, c->stream>>>(S);       // one resident block per SM: the spin barriers need co-residency
@@ -328,18 +373,32 @@ int comm_sync_items(Ctx *c)
     const size_t D = c->cfg.emb_dim, in4 = c->cfg.num_items * D / 4, wn4 = D * D / 4;
     float4 *delta = reinterpret_cast<float4 *>(c->delta);
     const int blocks = c->num_sms * 8;
-    delta_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->item_w), reinterpret_cast<const float4 *>(c->item_base), delta, in4);
-    delta_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->w0), reinterpret_cast<const float4 *>(c->w0_base), delta + in4, wn4);
     const size_t gn4 = c->item_g_base ? in4 : 0;
-    if (gn4) delta_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->item_g), reinterpret_cast<const float4 *>(c->item_g_base), delta + in4 + wn4, gn4);
-    HEAT_CUDA(cudaGetLastError());
-    HEAT_NCCL(api->AllReduce(c->delta, c->delta, (in4 + wn4 + gn4) * 4, ncclFloat, ncclSum, static_cast<ncclComm_t>(c->nccl_comm), c->stream));
-    const float scale = c->cfg.sync_average ? 1.0f / (float)c->world : 1.0f;
-    apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_w), reinterpret_cast<float4 *>(c->item_base), delta, scale, 0.f, in4);
-    apply_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->w0), reinterpret_cast<float4 *>(c->w0_base), delta + in4, scale, 0.f, wn4);
-    if (gn4) apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_g), reinterpret_cast<float4 *>(c->item_g_base), delta + in4 + wn4, scale, c->cfg.clip_val, gn4);
-    HEAT_CUDA(cudaGetLastError());
-    c->launches += gn4 ? 6 : 4;
+    const ncclComm_t comm = static_cast<ncclComm_t>(c->nccl_comm);
+    if (sync_mean(c)) {
+        // mean mode: new = (1/world) sum_q w_q (== base + mean of the deltas): all-reduce the arrays themselves
+        HEAT_CUDA(cudaMemcpyAsync(delta, c->item_w, in4 * 16, cudaMemcpyDeviceToDevice, c->stream));
+        HEAT_CUDA(cudaMemcpyAsync(delta + in4, c->w0, wn4 * 16, cudaMemcpyDeviceToDevice, c->stream));
+        if (gn4) HEAT_CUDA(cudaMemcpyAsync(delta + in4 + wn4, c->item_g, gn4 * 16, cudaMemcpyDeviceToDevice, c->stream));
+        HEAT_NCCL(api->AllReduce(c->delta, c->delta, (in4 + wn4 + gn4) * 4, ncclFloat, ncclSum, comm, c->stream));
+        const float scale = 1.0f / (float)c->world;
+        scale_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_w), delta, scale, 0.f, in4);
+        scale_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->w0), delta + in4, scale, 0.f, wn4);
+        if (gn4) scale_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_g), delta + in4 + wn4, scale, c->cfg.clip_val, gn4);
+        HEAT_CUDA(cudaGetLastError());
+        c->launches += gn4 ? 3 : 2;
+    } else {
+        delta_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->item_w), reinterpret_cast<const float4 *>(c->item_base), delta, in4);
+        delta_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->w0), reinterpret_cast<const float4 *>(c->w0_base), delta + in4, wn4);
+        if (gn4) delta_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<const float4 *>(c->item_g), reinterpret_cast<const float4 *>(c->item_g_base), delta + in4 + wn4, gn4);
+        HEAT_CUDA(cudaGetLastError());
+        HEAT_NCCL(api->AllReduce(c->delta, c->delta, (in4 + wn4 + gn4) * 4, ncclFloat, ncclSum, comm, c->stream));
+        apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_w), reinterpret_cast<float4 *>(c->item_base), delta, 1.0f, 0.f, in4);
+        apply_kernel<<<8, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->w0), reinterpret_cast<float4 *>(c->w0_base), delta + in4, 1.0f, 0.f, wn4);
+        if (gn4) apply_kernel<<<blocks, 256, 0, c->stream>>>(reinterpret_cast<float4 *>(c->item_g), reinterpret_cast<float4 *>(c->item_g_base), delta + in4 + wn4, 1.0f, c->cfg.clip_val, gn4);
+        HEAT_CUDA(cudaGetLastError());
+        c->launches += gn4 ? 6 : 4;
+    }
     c->syncs += 1;
     return 0;
 }
@@ -400,7 +459,8 @@ int local_group_sync(Ctx **cs, int n)
         S.gb[q] = grads ? reinterpret_cast<float4 *>(cs[q]->item_g_base) : nullptr;
     }
     const size_t D = c0->cfg.emb_dim;
-    S.scale = c0->cfg.sync_average ? 1.0f / (float)n : 1.0f;
+    S.scale = sync_mean(c0) ? 1.0f / (float)n : 1.0f;
+    S.mean = sync_mean(c0) ? 1 : 0;
     S.clip = c0->cfg.clip_val;
     S.n4_items = c0->cfg.num_items * D / 4; S.n4_w0 = D * D / 4;
     local_sync_kernel<<<c0->num_sms * 4, 256, 0, c0->stream>>>(S);

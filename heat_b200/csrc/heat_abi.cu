@@ -303,14 +303,15 @@ int heat_train_epoch(heat_ctx *ctx, double *mean_loss)
     // Multi-GPU: every rank runs the same number of segments (a collective follows each one), so
     // the count comes from the largest shard; a rank's segment i is its own [N*i/nseg, N*(i+1)/nseg).
     uint64_t nseg = 1;
-    if (c->world > 1 && c->sync_interval) {
+    if (c->world > 1) {
         if (c->nmax_for != N) {
             uint64_t nmax = N;
             int rc = comm_max_u64(c, &nmax);
             if (rc) return rc;
             c->nmax = nmax; c->nmax_for = N;
         }
-        nseg = std::max<uint64_t>(1, (c->nmax + c->sync_interval - 1) / c->sync_interval);
+        const uint64_t iv = sync_interval_of(c);
+        nseg = std::max<uint64_t>(1, (c->nmax + iv - 1) / iv);
     }
     if (int rc = need_seg_events(c, nseg)) return rc;
     // The whole epoch is queued on the stream -- segments and exchanges back to back -- and synchronised once: the
@@ -367,7 +368,8 @@ int heat_local_group_train_epoch(heat_ctx **ctxs, int n, double *mean_loss)
     HEAT_CUDA(cudaSetDevice(c0->device));
     uint64_t nmax = 0, total_n = 0;
     for (int q = 0; q < n; ++q) { lr_schedule(cs[q]); nmax = std::max(nmax, cs[q]->n_samples); total_n += cs[q]->n_samples; }
-    const uint64_t nseg = c0->sync_interval ? std::max<uint64_t>(1, (nmax + c0->sync_interval - 1) / c0->sync_interval) : 1;
+    const uint64_t iv = sync_interval_of(c0);
+    const uint64_t nseg = std::max<uint64_t>(1, (nmax + iv - 1) / iv);
     if (int rc = need_seg_events(c0, nseg)) return rc;
     for (int q = 0; q < n; ++q) HEAT_CUDA(cudaMemsetAsync(cs[q]->loss_sum, 0, sizeof(double), cs[q]->stream));
     float k_ms = 0.f, x_ms = 0.f;

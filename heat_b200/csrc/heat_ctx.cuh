@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <algorithm>
 #include <string>
 #include <vector>
 #include "../../include/heat_b200.h"
@@ -72,6 +73,13 @@ int fail(const std::string &msg);
         if (_e != cudaSuccess)                                                                   \
             return ::heat::fail(std::string(#expr) + ": " + cudaGetErrorString(_e));             \
     } while (0)
+
+// multi-GPU exchange policy (heat_config.sync_average, heat_set_sync_interval): the documented defaults
+inline bool sync_mean(const Ctx *c) { return c->cfg.sync_average != 2; }
+inline uint64_t sync_interval_of(const Ctx *c)
+{
+    return c->sync_interval ? c->sync_interval : std::max<uint64_t>(65536, 3 * c->cfg.num_items);
+}
 
 // hot-tile sampler fields of a kernel parameter block from the config (tile_sampler && neg_sampler == 1), else uniform
 template <class Params> inline void set_sampler(const Ctx *c, Params &P)

@@ -2,6 +2,7 @@
 #include "heat_ctx.cuh"
 #include "train_kernel.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include "train_kernel_cta.cuh"
 
 namespace heat {
@@ -145,6 +146,14 @@ int check_range(Ctx *c, uint64_t begin, uint64_t end)
     return 0;
 }
 
+// Experiment knob (tools/concurrency_exp.py): HEAT_EXP_LR_W0_SCALE scales the aggregator's learning rate, 0 freezes W0.
+// Unset = 1: the product path is unchanged.
+float exp_lr_w0_scale()
+{
+    static const float v = [] { const char *e = std::getenv("HEAT_EXP_LR_W0_SCALE"); return e && *e ? (float)std::atof(e) : 1.0f; }();
+    return v;
+}
+
 // kernel parameter block of local samples [begin,end) with the given scratch words
 TrainParams make_params(Ctx *c, uint64_t begin, uint64_t end, unsigned long long *counter, double *loss_sum, float *loss_out)
 {
@@ -160,7 +169,7 @@ TrainParams make_params(Ctx *c, uint64_t begin, uint64_t end, unsigned long long
     P.chunk = (int)c->cfg.chunk;
     P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
     P.upd = (int)c->cfg.update_mode;
-    P.lr = c->l_r; P.lr_w0 = c->cfg.l_r; P.clip = c->cfg.clip_val;
+    P.lr = c->l_r; P.lr_w0 = c->cfg.l_r * exp_lr_w0_scale(); P.clip = c->cfg.clip_val;
     P.no_cache = c->cfg.history_mode == 1;
     return P;
 }

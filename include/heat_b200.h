@@ -59,8 +59,10 @@ typedef struct heat_config {
     uint32_t update_mode;       /* item-row write-back in the Hogwild grid: 0 store the stepped snapshot (the
                                    reference's sequence), 1 re-read the rows right before the step, 2 apply the
                                    step as L2 vector reductions (no lost updates). deterministic=1 forces 0 */
-    uint32_t sync_average;      /* multi-GPU item/W0 reconciliation: 0 base += sum of rank deltas (default),
-                                   1 base += mean of rank deltas (the fork's averaging, engine.cpp:371-373) */
+    uint32_t sync_average;      /* multi-GPU item/W0 reconciliation: 0 = default = 1: every replica becomes the MEAN of the
+                                   replicas (== base + mean of the rank deltas: the fork's averaging, engine.cpp:354-375);
+                                   2: base + SUM of the rank deltas.  The mean keeps Recall@20 on the one-GPU run's for every
+                                   exchange interval from 1/74 to 1/10 of an epoch; the sum does not */
     uint32_t history_mode;      /* 0 default: the history column sums are gathered once per run of a user's
                                    consecutive samples and patched with the exact change of the rows the warp
                                    rewrites; 1: re-gathered for every sample (the reference's literal sequence) */
@@ -213,7 +215,10 @@ int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[1
  * (engine.cpp:148-152,262-286,354-375): one all-reduce of the item-table delta and one of
  * the W0 delta since the last sync; every rank ends with base + sum of deltas. */
 int heat_comm_sync_items(heat_ctx *ctx);
-int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);   /* 0 = once per epoch */
+/* samples a rank trains between two exchanges.  0 (the initial value) = auto: max(65536, 3 x num_items) -- every item row
+ * is touched ~50 times per replica between exchanges, 10 exchanges per epoch at the Amazon-Books shape; any value >= the
+ * shard size = once per epoch.  Every rank must set the same value. */
+int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);
 /* exchanges of the last heat_train_epoch and their total device time (CUDA events on the context's stream), ms */
 int heat_last_exchange(heat_ctx *ctx, uint64_t *count, float *ms);
 /* Multi-rank emulation on ONE device, for convergence tests and interval studies on a single-GPU box: n contexts

@@ -1,13 +1,16 @@
-"""Multi-GPU check of the fused peer-memory exchange (comm.cu: peer_sync_kernel) against the NCCL path.
+"""Multi-GPU check of the fused peer-memory exchange (comm.cu: peer_sync_kernel): against the NCCL path, and against the
+single-device rank emulation (heat_local_group_*).  Run by tests/test_multigpu_gpu.py when >= 2 GPUs are visible.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29533 tools/check_peer_sync.py
 
-Every rank trains the same small shard layout twice from identical tables in deterministic mode (one block, file
-order: bit-reproducible), once with exchange_mode 0 (fused kernel over CUDA-IPC peer memory) and once with
-exchange_mode 1 (delta kernel + ncclAllReduce + apply kernel), two exchanges per epoch, two epochs.  At N = 2 the
-two sums are the same two addends, so the tables must agree BIT FOR BIT; at N > 2 the summation order differs and
-they must agree to 1e-6 relative.  Also: all ranks end with identical item tables, and the exchange time of both
-paths at the Amazon-Books table size is printed."""
+Every rank trains its own small shard twice from identical tables in deterministic mode (one block, file order:
+bit-reproducible), once with exchange_mode 0 (fused kernel over CUDA-IPC peer memory) and once with exchange_mode 1
+(NCCL all-reduce path), two exchanges per epoch, two epochs, for both reconciliation rules (mean of the replicas /
+sum of the rank deltas).  At N = 2 a sum has two addends, so the two paths must agree BIT FOR BIT; at N > 2 NCCL's
+summation order differs and they must agree to 1e-6 relative.  The fused kernel adds in rank order, exactly as the
+emulation group does, so rank 0 re-runs all N ranks as an emulation group on its own GPU and the tables must be
+bit-identical at every N.  All ranks must end with identical item tables.  The exchange time of both paths at the
+Amazon-Books table size is printed."""
 import os
 import sys
 import time
@@ -19,17 +22,24 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from heat_b200 import abi, synth
 
+N_SAMPLES = 12000
 
-def make(rank, world, mode, d, tables, **kw):
-    ctx = abi.Context(64, 16, d.num_users, d.num_items, seed=2022, sample_offset=rank * d.train_size, device=rank,
-                      exchange_mode=mode, **kw)
+
+def shard_of(q):
+    return synth.generate(600, 900, N_SAMPLES, seed=100 + q)          # rank q: its own users, the shared item ids
+
+
+def make(rank, world, mode, d, tables, connect=True, device=None, **kw):
+    ctx = abi.Context(64, 16, d.num_users, d.num_items, seed=2022, sample_offset=rank * d.train_size,
+                      device=rank if device is None else device, exchange_mode=mode, **kw)
     ctx.set_dataset(d.clicks, d.his_items, d.masks)
     ctx.bind_tables(*tables)
-    uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
-    if rank == 0:
-        uid.copy_(torch.from_numpy(abi.Context.comm_unique_id()))
-    dist.broadcast(uid, 0)
-    ctx.comm_init(rank, world, uid.cpu().numpy())
+    if connect:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.from_numpy(abi.Context.comm_unique_id()))
+        dist.broadcast(uid, 0)
+        ctx.comm_init(rank, world, uid.cpu().numpy())
     return ctx
 
 
@@ -37,32 +47,52 @@ def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
-    d = synth.generate(600, 900, 12000, seed=100 + rank)          # every rank: its own users, the shared item ids
+    d = shard_of(rank)
     init = synth.init_tables(d.num_users, d.num_items, 64, seed=7)
-    out = {}
-    for mode in (0, 1):
-        t = [a.copy() for a in init]
-        ctx = make(rank, world, mode, d, t, deterministic=True)
-        ctx.set_sync_interval(d.train_size // 2 + 1)
-        want = 2 if mode == 0 else 1
-        assert ctx.comm_mode() == want, f"rank {rank}: comm_mode {ctx.comm_mode()} (expected {want})"
-        losses = [ctx.train_epoch() for _ in range(2)]
-        ctx.sync_to_host()
-        out[mode] = (t[1].copy(), t[2].copy(), losses)
-        ctx.close()
-    iw0, w00, l0 = out[0]
-    iw1, w01, l1 = out[1]
-    if world == 2:
-        assert np.array_equal(iw0, iw1) and np.array_equal(w00, w01), "fused exchange differs from the NCCL path"
-        assert l0 == l1
-    else:
-        assert np.abs(iw0 - iw1).max() <= 1e-6 * np.abs(iw1).max() and np.abs(w00 - w01).max() <= 1e-6 * np.abs(w01).max()
-    g = torch.from_numpy(iw0).cuda()
-    ref = g.clone()
-    dist.broadcast(ref, 0)
-    assert torch.equal(g, ref), "replicas differ after the fused exchange"
+    interval = N_SAMPLES // 2 + 1
+    for avg, grads in ((1, 0), (2, 0), (2, 1)):
+        out = {}
+        for mode in (0, 1):
+            t = [a.copy() for a in init]
+            ctx = make(rank, world, mode, d, t, deterministic=True, sync_average=avg, sync_grads=grads)
+            ctx.set_sync_interval(interval)
+            want = 2 if mode == 0 else 1
+            assert ctx.comm_mode() == want, f"rank {rank}: comm_mode {ctx.comm_mode()} (expected {want})"
+            losses = [ctx.train_epoch() for _ in range(2)]
+            assert ctx.last_exchange()[0] == 2
+            ctx.sync_to_host()
+            out[mode] = (t[1].copy(), t[2].copy(), losses)
+            ctx.close()
+        iw0, w00, l0 = out[0]
+        iw1, w01, l1 = out[1]
+        if world == 2:
+            assert np.array_equal(iw0, iw1) and np.array_equal(w00, w01), "fused exchange differs from the NCCL path"
+            assert l0 == l1
+        else:
+            assert np.abs(iw0 - iw1).max() <= 1e-6 * np.abs(iw1).max() and np.abs(w00 - w01).max() <= 1e-6 * np.abs(w01).max()
+        g = torch.from_numpy(iw0).cuda()
+        ref = g.clone()
+        dist.broadcast(ref, 0)
+        assert torch.equal(g, ref), "replicas differ after the fused exchange"
+        if rank == 0:           # the same N ranks as an emulation group on this GPU: same arithmetic, same order
+            ctxs, keep = [], []
+            for q in range(world):
+                dq = shard_of(q)
+                tq = [a.copy() for a in synth.init_tables(dq.num_users, dq.num_items, 64, seed=7)]
+                keep.append(tq)
+                c = make(q, world, 0, dq, tq, connect=False, device=0, deterministic=True, sync_average=avg, sync_grads=grads)
+                c.set_sync_interval(interval)
+                ctxs.append(c)
+            grp = abi.LocalGroup(ctxs)
+            el = [grp.train_epoch() for _ in range(2)]
+            ctxs[0].sync_to_host()
+            assert np.array_equal(keep[0][1], iw0) and np.array_equal(keep[0][2], w00), "emulation group differs from the real ranks"
+            assert np.allclose(el, l0, rtol=1e-12), (el, l0)
+            for c in ctxs:
+                c.close()
+        dist.barrier()
 
-    # exchange time at the Amazon-Books table size (91 599 x 64 fp32 + W0), both paths
+    # exchange time at the Amazon-Books table size (91 599 x 64 fp32 + W0), both paths, default rule (mean)
     big = synth.generate(64, 91599, 4096, seed=3)
     for mode in (0, 1):
         t = list(synth.init_tables(big.num_users, big.num_items, 64, seed=7))
@@ -80,7 +110,7 @@ def main():
             print(f"exchange of 23.4 MB at world {world}: {'fused peer kernel' if mode == 0 else 'NCCL all-reduce path'} {ms:.3f} ms", flush=True)
         ctx.close()
     if rank == 0:
-        print(f"peer exchange check ok at world {world}: bit-identical to the NCCL path" if world == 2 else f"peer exchange check ok at world {world}", flush=True)
+        print(f"peer exchange check ok at world {world}", flush=True)
     dist.destroy_process_group()
 
 

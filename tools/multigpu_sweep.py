@@ -6,7 +6,7 @@ The dataset is the weak-scaling form of <shape>: <world> x the users over the sa
 trained (a) by one context over all users ("n1": what --gpus 1 would do with this data), (b) by <world> contexts, one
 user-range shard each, as an emulation group (heat_local_group_*: the ranks' segments one after the other, then the
 same reconciliation a real run does).  A policy is `interval:average:grads[:engine[:share]]` -- samples per rank between
-exchanges (0 = once per epoch), 0 sum / 1 mean of the rank deltas, 1 = grad rows exchanged too.  --ref adds the CPU
+exchanges (0 = once per epoch), 0/1 mean of the replicas, 2 sum of the rank deltas, 1 = grad rows exchanged too.  --ref adds the CPU
 reference (oracle/_ref, all host threads) on the union.  Prints per-epoch losses and Recall@20 of every arm.
 """
 import json
@@ -22,6 +22,8 @@ args = [a for a in sys.argv[1:] if not a.startswith("--")]
 flags = [a for a in sys.argv[1:] if a.startswith("--")]
 name, world, epochs = args[0], int(args[1]), int(args[2])
 policies = args[3:]
+repeat = max([int(f.split("=")[1]) for f in flags if f.startswith("--repeat=")] or [1])
+policies = [p for p in policies for _ in range(repeat)]
 D, K = 64, 16
 clip = 0.1 if name == "gowalla" else 1.0
 t0 = time.time()
