@@ -200,7 +200,7 @@ def cpu_baseline(w, d, tables, budget_s=12.0):
            "sample": f"first {n} of {d.train_size} samples, 1 pass, {secs[0]:.2f} s, OpenMP schedule(dynamic,512), build B (-O3)",
            "loss": loss}
     if kind == "reference" and oracle.RefOracle.available("O0"):
-        nA = max(n0 // 4, int(min(n, rate * budget_s / 12)))               # the unoptimised build is ~10x slower
+        nA = max(n0 // 5, int(min(n, rate * 4.0 / 30)))                     # the unoptimised build is ~30x slower: ~4 s of work
         sA, _, _, _ = cpu_reference_run(w, d, tables, nA, 1, thr, opt="O0")
         out["build_A_reference_flags"] = {"value": nA / sA[0], "unit": UNIT, "cores": nthr,
                                           "sample": f"first {nA} samples, 1 pass, {sA[0]:.2f} s, the reference's own flags (no -O)"}
@@ -382,28 +382,31 @@ def run_gpu_arm(args, rank, world, local_rank):
                            "fp32_equivalent_tflops": flops / (ev_ms_max * 1e-3) / 1e12}}
     ctx.close()
 
-    # ---- throughput mode, reported beside the headline: the warp-per-sample kernel on a full grid (thousands of
-    #      samples in flight).  Faster, but its Hogwild dynamics leave the reference's Recall@20,
-    #      so it is not the configuration `value` is quoted on.
+    # ---- strict mode, reported beside the headline: the CTA-per-sample kernel (engine 2) at one sample in flight per
+    #      ~600 item rows keeps the per-epoch LOSS within 0.03 of the reference in every epoch as well (the default engine
+    #      keeps Recall@20, its loss trails in the first epochs: DESIGN.md section 6).
     thr = None
-    if args.engine == 0 and engine_ran == 2 and world == 1 and not args.no_throughput_mode:
+    if args.engine == 0 and engine_ran == 1 and world == 1 and not args.no_strict_mode:
         for t, t0_ in zip((uw, iw, w0), init):
             t[...] = t0_
-        ctx2 = new_context(abi, w, d, args, off, local_rank, engine=1)
+        ctx2 = new_context(abi, w, d, args, off, local_rank, engine=2)
         ctx2.set_dataset(clicks, his, masks)
         ctx2.bind_tables(uw, iw, w0)
-        for _ in range(args.warmup):
-            flush_l2(); ctx2.train_epoch()
-        barrier()
-        ms2, k2 = [], []
-        for _ in range(args.steps):
-            flush_l2(); ctx2.train_epoch()
-            ms2.append(ctx2.last_epoch_ms()); k2.append(ctx2.last_kernel_ms())
-        barrier()
-        tot2 = float(np.sum(ms2))
-        thr = {"value": N * args.steps / (tot2 * 1e-3), "unit": UNIT, "ms_per_step": tot2 / args.steps,
-               "kernel": "heat::train_kernel (warp per sample, full grid)", "kernel_ms": float(np.mean(k2)),
-               "recall_parity": "outside the 0.005 tolerance (DESIGN.md section 6)"}
+        try:
+            for _ in range(args.warmup):
+                flush_l2(); ctx2.train_epoch()
+            barrier()
+            ms2, k2 = [], []
+            for _ in range(args.steps):
+                flush_l2(); ctx2.train_epoch()
+                ms2.append(ctx2.last_epoch_ms()); k2.append(ctx2.last_kernel_ms())
+            barrier()
+            tot2 = float(np.sum(ms2))
+            thr = {"value": N * args.steps / (tot2 * 1e-3), "unit": UNIT, "ms_per_step": tot2 / args.steps,
+                   "kernel": "heat::train_cta_kernel (CTA per sample, one sample in flight per ~600 item rows)", "kernel_ms": float(np.mean(k2)),
+                   "parity": "per-epoch loss within 0.03 and Recall@20 within 0.005 of the reference (tests/test_recall_parity_gpu.py, engine 2)"}
+        except abi.HeatError as e:
+            thr = {"unavailable": str(e)}
         ctx2.close()
 
     # ---- convergence at N > 1: a fresh N-rank run with this exchange policy against ONE GPU training the same union
@@ -450,7 +453,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     achieved = alg / (k_ms * 1e-3) / 1e9
     table_bytes = 2 * (d.num_users + d.num_items) * D * 4
     kernel = {1: "heat::train_kernel", 2: "heat::train_cta_kernel", 3: "heat::train_bigk_kernel"}.get(engine_ran, "?")
-    cap = {2: "r01_train_cta_kernel_ncu_raw.csv", 1: "r01_train_kernel_ncu_raw.csv", 3: "r01_bigk_kernel_ncu_raw.csv"}.get(engine_ran)
+    cap = {2: "r01_train_cta_kernel_ncu_raw.csv", 1: "r02_train_kernel_ncu_raw.csv", 3: "r01_bigk_kernel_ncu_raw.csv"}.get(engine_ran)
     traffic = args.ncu_traffic if args.ncu_traffic is not None else (ncu_traffic(cap) if cap and args.workload in ("amazon-book", "cfg4") else None)
     roofline = {"kernel": kernel, "kernel_ms": k_ms, "launches_per_step": max(1, int(xch_n)) if world > 1 else 1,
                 "algorithmic_bytes_per_step": alg, "achieved": achieved, "unit": "GB/s",
@@ -480,7 +483,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                     "what": "heat_set_dataset + heat_upload_tables + heat_train_epoch + heat_sync_to_host from pinned host buffers"},
             "roofline": roofline, "loss_first_last": [losses[0], losses[-1]], "wall_s_timed_region": wall,
             "update_mode": args.update_mode,
-            "engine": {1: "warp-per-sample kernel", 2: "CTA-per-sample kernel", 3: "large-negative kernel"}.get(engine_ran, "?") +
+            "engine": {1: "warp-per-sample kernel, fresh-grad update, full grid", 2: "CTA-per-sample kernel", 3: "large-negative kernel"}.get(engine_ran, "?") +
                       (" (engine 0 = auto)" if args.engine == 0 else " (forced)")}
     if world > 1:
         line.update({"sync_interval": args.sync_interval, "sync_average": args.sync_average, "sync_grads": args.sync_grads,
@@ -493,8 +496,9 @@ def run_gpu_arm(args, rank, world, local_rank):
         line["convergence"] = conv
         line["recall_vs_n1"] = conv.get("recall_vs_n1")
     if thr is not None:
-        thr["l2_frac"] = alg / (thr["kernel_ms"] * 1e-3) / 1e9 / roofline["peak"] if roofline["bound"] == "l2" else None
-        line["throughput_mode"] = thr
+        if "kernel_ms" in thr:
+            thr["l2_frac"] = alg / (thr["kernel_ms"] * 1e-3) / 1e9 / roofline["peak"] if roofline["bound"] == "l2" else None
+        line["strict_mode"] = thr
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(w, d, init, args.cpu_seconds)
     print(json.dumps(line), file=_JSON_OUT, flush=True)
@@ -515,7 +519,7 @@ def main():
     ap.add_argument("--max-blocks", type=int, default=0)
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--engine", type=int, default=0, help="0 auto, 1 warp-per-sample, 2 CTA-per-sample, 3 large-negative")
-    ap.add_argument("--no-throughput-mode", action="store_true", help="skip the extra warp-per-sample full-grid measurement")
+    ap.add_argument("--no-strict-mode", action="store_true", help="skip the extra measurement of the loss-strict CTA-per-sample engine")
     ap.add_argument("--sync-interval", type=int, default=DEFAULT_SYNC["interval"], help="samples per GPU between exchanges of the replicated item table (0 = auto: max(65536, 3 x items))")
     ap.add_argument("--sync-average", type=int, default=DEFAULT_SYNC["average"], help="0/1 mean of the replicas (the fork's averaging; default), 2 sum of the rank deltas")
     ap.add_argument("--sync-grads", type=int, default=DEFAULT_SYNC["grads"], help="1 = the persistent item grad rows are exchanged too")

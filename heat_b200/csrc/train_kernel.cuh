@@ -54,8 +54,10 @@ constexpr unsigned FULL = 0xffffffffu;
 //   UPD_STORE  the reference's own sequence (matrix_factorization.cpp:133-149,169-174): the row
 //              snapshot taken at gather time is stepped and stored.  Exact in sequential order;
 //              under thousands of concurrent warps the long read-modify-write window loses updates.
-//   UPD_FRESH  the rows are re-read immediately before the step, so the window shrinks from the
-//              whole sample (~9 us) to one L2 round trip.  Same result as UPD_STORE when nothing races.
+//   UPD_FRESH  the GRAD rows are read only right before the step (g = clamp(g_now + dg), stored) and the
+//              weight rows are stepped by an L2 vector reduction (w += -lr*g): the read-modify-write
+//              window of g shrinks from the whole sample to one L2 round trip and no weight step is ever
+//              lost.  Same result as UPD_STORE when nothing races (up to the rounding of w - lr*g).
 //   UPD_ATOMIC the step is applied as an L2 vector reduction (w += -lr*g_new, g += g_new - g_old):
 //              no update is ever lost, whatever the concurrency.
 enum { UPD_STORE = 0, UPD_FRESH = 1, UPD_ATOMIC = 2 };
@@ -221,8 +223,16 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
     float *W0s = smem;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane / VL, sl = lane % VL;
-    float *ring = smem + D * D + warp * (32 * 2 * D);
-    unsigned *hfilter = reinterpret_cast<unsigned *>(smem + D * D + WARPS * (32 * 2 * D)) + warp * 64;   // CACHE: 2048-bit filter
+    // W0 gradients: (mean, 0.6 g_u) pairs of the CTA's samples go into ONE ring of two 32-slot halves shared by its
+    // warps; the warp that completes a half applies it (behavior_aggregators.cpp:141-146 with the CTA in the role of the
+    // OpenMP thread).  Pending, unapplied gradients are then <= 64 per CTA whatever the number of warps, as in the
+    // CTA-per-sample kernel -- with one ring per WARP a full grid holds ~28 000 of them, and the loss follows
+    // (DESIGN.md section 6).
+    float *ring = smem + D * D;                                   // [64][2D]
+    float *wscr = ring + 64 * 2 * D + warp * D;                   // this warp's staging of the history mean (GEMV operand)
+    unsigned *rctl = reinterpret_cast<unsigned *>(ring + 64 * 2 * D + WARPS * D);   // [0] slots claimed, [1] slots applied, [2..3] written per half
+    unsigned *hfilter = rctl + 4 + warp * 64;                     // CACHE: 2048-bit filter
+    if (threadIdx.x < 4) rctl[threadIdx.x] = 0u;
 
     for (int i = threadIdx.x * 4; i < D * D; i += WARPS * 32 * 4)
         *reinterpret_cast<float4 *>(W0s + i) = ldcg4(P.w0 + i);
@@ -232,7 +242,6 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
     const float omg = 1.0f - gamma;
     const float score_mul = (float)(1.0 / 0.07);     // matrix_factorization.cpp:101
     const int K = P.K;
-    unsigned iter = 0;                               // BehaviorAggregator::iteration of this warp
     double loss_acc = 0.0;
     const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
 
@@ -351,7 +360,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             }
             const float rH = (float)(1.0 / (double)H);     // behavior_aggregators.cpp:63
             const float4 mean = rH * acc;
-            float *ms = ring + (iter & 31) * 2 * D;
+            float *ms = wscr;
             if (g == 0) *reinterpret_cast<float4 *>(ms + 4 * sl) = mean;
             __syncwarp();
 
@@ -438,22 +447,18 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
                     }
                 }
                 if (UPD == UPD_FRESH) {
-                    // second look at the rows, right before the step: all loads first, then the stores
-                    float4 fw[NJ], fg[NJ];
+                    // the grad rows as they are NOW, right before the step: all loads first, then the stores; the weight
+                    // rows take their step as a reduction at L2 and are not read again
+                    float4 fg[NJ];
 #pragma unroll
-                    for (int j = 0; j < NJ; ++j) {
-                        if (j * R + g < K) {
-                            fw[j] = ldcg4(P.item_w + (size_t)nid[j] * D + 4 * sl);
-                            fg[j] = ldcg4(P.item_g + (size_t)nid[j] * D + 4 * sl);
-                        }
-                    }
+                    for (int j = 0; j < NJ; ++j)
+                        if (j * R + g < K) fg[j] = ldcg4(P.item_g + (size_t)nid[j] * D + 4 * sl);
 #pragma unroll
                     for (int j = 0; j < NJ; ++j) {
                         if (j * R + g < K) {
                             float4 gk = fg[j] + dl[j];
                             gk = clamp4(gk, P.clip);
-                            fma4(fw[j], -P.lr, gk);
-                            stcg4(P.item_w + (size_t)nid[j] * D + 4 * sl, fw[j]);
+                            red4(P.item_w + (size_t)nid[j] * D + 4 * sl, (-P.lr) * gk);
                             stcg4(P.item_g + (size_t)nid[j] * D + 4 * sl, gk);
                         }
                     }
@@ -491,18 +496,39 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             float4 gp = gp_old;
             fma4(gp, lgsum, gp_p);
 
-            // ---- aggregator backward (behavior_aggregators.cpp:129-153)
-            if (g == 0) *reinterpret_cast<float4 *>(ms + D + 4 * sl) = omg * gu;
-            iter += 1;                                         // forward's iteration += 1 (:124)
-            __syncwarp();
-            if ((iter & 31) == 0) { w0_flush<D>(ring, W0s, P.w0, 32, P.lr_w0, lane); __syncwarp(); }
+            // ---- aggregator backward (behavior_aggregators.cpp:129-153): this sample's (mean, 0.6 g_u) pair goes into the
+            //      CTA's ring; the warp that completes a half of 32 applies it (forward's iteration += 1, :124)
+            {
+                unsigned idx = 0;
+                if (lane == 0) {
+                    idx = atomicAdd(&rctl[0], 1u);
+                    while (idx - *reinterpret_cast<volatile unsigned *>(&rctl[1]) >= 64u) { }   // the half is still being applied (rare)
+                }
+                idx = __shfl_sync(FULL, idx, 0);
+                float *slot_ = ring + (idx & 63u) * 2 * D;
+                if (g == 0) {
+                    *reinterpret_cast<float4 *>(slot_ + 4 * sl) = mean;
+                    *reinterpret_cast<float4 *>(slot_ + D + 4 * sl) = omg * gu;
+                }
+                __syncwarp();
+                const unsigned half = (idx >> 5) & 1u;
+                unsigned done = 0;
+                if (lane == 0) { __threadfence_block(); done = atomicAdd(&rctl[2 + half], 1u) + 1u; }
+                done = __shfl_sync(FULL, done, 0);
+                if (done == 32u) {                             // exactly one warp per completed half
+                    __threadfence_block();
+                    w0_flush<D>(ring + half * 32 * 2 * D, W0s, P.w0, 32, P.lr_w0, lane);
+                    __syncwarp();
+                    if (lane == 0) { rctl[2 + half] = 0u; __threadfence_block(); atomicAdd(&rctl[1], 32u); }
+                    __syncwarp();
+                }
+            }
             gu = gamma * gu;
 
             // ---- user / positive step and write-back (matrix_factorization.cpp:166-174)
             gu = clamp4(gu, P.clip);
             fma4(ua, -P.lr, gu);
             float *prow = P.item_w + (size_t)p * D + 4 * sl, *pgrow = P.item_g + (size_t)p * D + 4 * sl;
-            static_assert(!(CACHE && UPD == UPD_FRESH), "the run cache needs the positive row's own delta");
             if (UPD == UPD_STORE) {
                 gp = clamp4(gp, P.clip);
                 fma4(pw, -P.lr, gp);
@@ -513,14 +539,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
                 if (R == 1 || g == 0) red4(prow, (-P.lr) * gp);
                 if (R == 1 || g == 1) red4(pgrow, gp - gp_old);
             } else {
-                if (g == 0) {
-                    float4 fw = ldcg4(prow), fg = ldcg4(pgrow);
-                    fma4(fg, lgsum, gp_p);
-                    fg = clamp4(fg, P.clip);
-                    fma4(fw, -P.lr, fg);
-                    stcg4(prow, fw);
-                    stcg4(pgrow, fg);
-                }
+                // UPD_FRESH: every row group reads the grad row as it is now (the run cache needs the applied step on all lanes)
+                gp = ldcg4(pgrow);
+                fma4(gp, lgsum, gp_p);
+                gp = clamp4(gp, P.clip);
+                if (R == 1 || g == 0) red4(prow, (-P.lr) * gp);
+                if (R == 1 || g == 1) stcg4(pgrow, gp);
             }
             if (R == 1 || g == 0) stcg4(P.user_w + (size_t)u * D + 4 * sl, ua);
             if (R == 1 || g == 1) stcg4(P.user_g + (size_t)u * D + 4 * sl, gu);
@@ -533,8 +557,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
             loss_acc += (double)loss;
         }
     }
-    __syncwarp();
-    if (!P.drop_w0_tail && (iter & 31) != 0) w0_flush<D>(ring, W0s, P.w0, (int)(iter & 31), P.lr_w0, lane);
+    // ---- the leftover (< 32) pairs of the half that was being filled (the reference drops a partial batch: drop_w0_tail)
+    __syncthreads();
+    if (warp == 0 && !P.drop_w0_tail) {
+        const unsigned claimed = rctl[0], applied = rctl[1];
+        if (claimed > applied) w0_flush<D>(ring + ((applied >> 5) & 1u) * 32 * 2 * D, W0s, P.w0, (int)(claimed - applied), P.lr_w0, lane);
+    }
     if (lane == 0 && loss_acc != 0.0) atomicAdd(P.loss_sum, loss_acc);
 }
 

@@ -13,7 +13,7 @@ template <int D, int NJ, int WARPS, bool PRELOAD_G, int UPD = UPD_STORE, bool CA
 int launch_one(Ctx *c, const TrainParams &P, int blocks)
 {
     auto kern = train_kernel<D, NJ, WARPS, PRELOAD_G, UPD, CACHE>;
-    const size_t smem = (size_t)(D * D + WARPS * 32 * 2 * D) * sizeof(float) + (size_t)WARPS * 64 * sizeof(unsigned);   // W0, rings, history filters
+    const size_t smem = (size_t)(D * D + 64 * 2 * D + WARPS * D) * sizeof(float) + (size_t)(4 + WARPS * 64) * sizeof(unsigned);   // W0, the CTA's gradient ring, per-warp mean staging, ring counters, history filters
     HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
     kern<<<blocks, WARPS * 32, smem, c->stream>>>(P);
@@ -48,10 +48,10 @@ int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
     const int bps = c->cfg.blocks_per_sm ? (int)c->cfg.blocks_per_sm : 1;
     int blocks = deterministic ? 1 : c->num_sms * bps;
     if (c->cfg.max_blocks && blocks > (int)c->cfg.max_blocks) blocks = (int)c->cfg.max_blocks;
-    // engine 0 (auto) without an explicit max_blocks: samples in flight scale with the item table, about one per
+    // without an explicit max_blocks / blocks_per_sm: samples in flight scale with the item table, about one per
     // 600 item rows, which keeps the chance that two samples in flight share a row where the reference's
-    // 16-128 threads have it (Recall@20 within 0.005 of the reference at this setting)
-    if (!deterministic && !c->cfg.max_blocks && c->cfg.engine == 0) {
+    // 16-128 threads have it (loss within 0.03 and Recall@20 within 0.005 of the reference)
+    if (!deterministic && !c->cfg.max_blocks && c->cfg.blocks_per_sm == 0) {
         const int cap = (int)std::max<uint64_t>(8, c->cfg.num_items / 600);
         if (blocks > cap) blocks = cap;
     }
@@ -64,6 +64,16 @@ int dispatch_cta(Ctx *c, const TrainParams &P, bool deterministic)
     return -1;
 }
 
+// Default bound on the Hogwild concurrency of the warp-per-sample kernel (no explicit max_blocks): at most one warp in
+// flight per 16 item rows.  The BASELINE shapes (38 k - 2 M items) run the full grid; a toy table of a few hundred rows
+// is not hammered by 1 776 concurrent samples.
+int cap_blocks(const Ctx *c, int blocks, int warps)
+{
+    if (c->cfg.max_blocks || c->cfg.deterministic) return blocks;
+    const int cap = (int)std::max<uint64_t>(1, c->cfg.num_items / 16 / (uint64_t)warps);
+    return std::min(blocks, cap);
+}
+
 // Pick the instantiation for (D, K, warps).  K must fit the register-resident path:
 // K <= NJ * 32/(D/4).
 int dispatch(Ctx *c, const TrainParams &P, bool deterministic, int warps_override = 0)
@@ -73,13 +83,18 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic, int warps_overrid
     const int bps = c->cfg.blocks_per_sm ? (int)c->cfg.blocks_per_sm : 1;
     int blocks = deterministic ? 1 : c->num_sms * bps;
     if (c->cfg.max_blocks && blocks > (int)c->cfg.max_blocks) blocks = (int)c->cfg.max_blocks;
-    const int upd = deterministic ? (int)UPD_STORE : P.upd;
+    // heat_config.update_mode: 0 (default) and 1 = UPD_FRESH, 2 = UPD_ATOMIC, 3 = UPD_STORE; one warp in file order
+    // (deterministic) always runs the reference's own store sequence
+    const int upd = deterministic ? (int)UPD_STORE : (P.upd == 2 ? (int)UPD_ATOMIC : P.upd == 3 ? (int)UPD_STORE : (int)UPD_FRESH);
     const bool cache = c->cfg.history_mode != 1;          // 0 default: run cache; 1: re-gather every sample
 #define HEAT_LAUNCH(D_, NJ_, W_, PG_) return launch_one<D_, NJ_, W_, PG_>(c, P, blocks)
 // Hogwild grid: the three item-row update modes of train_kernel.cuh
 #define HEAT_LAUNCH_UPD(D_, NJ_, W_, PG_)                                                   \
     do {                                                                                    \
-        if (upd == UPD_FRESH) return launch_one<D_, NJ_, W_, false, UPD_FRESH>(c, P, blocks); \
+        if (upd == UPD_FRESH) {                                                             \
+            if (cache) return launch_one<D_, NJ_, W_, false, UPD_FRESH, true>(c, P, blocks); \
+            return launch_one<D_, NJ_, W_, false, UPD_FRESH>(c, P, blocks);                  \
+        }                                                                                   \
         if (cache) {                                                                        \
             if (upd == UPD_ATOMIC) return launch_one<D_, NJ_, W_, PG_, UPD_ATOMIC, true>(c, P, blocks); \
             return launch_one<D_, NJ_, W_, PG_, UPD_STORE, true>(c, P, blocks);             \
@@ -90,20 +105,24 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic, int warps_overrid
     if (D == 64 && K <= 16) {
         if (deterministic) { if (cache) return launch_one<64, 8, 1, true, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(64, 8, 1, true); }
         if (warps == 0) warps = 12;
+        blocks = cap_blocks(c, blocks, warps <= 4 ? 4 : warps <= 8 ? 8 : 12);
         if (warps <= 4) HEAT_LAUNCH_UPD(64, 8, 4, true);
         if (warps <= 8) HEAT_LAUNCH_UPD(64, 8, 8, true);
         HEAT_LAUNCH_UPD(64, 8, 12, true);
     }
     if (D == 64 && K <= 32) {
         if (deterministic) { if (cache) return launch_one<64, 16, 1, false, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(64, 16, 1, false); }
+        blocks = cap_blocks(c, blocks, 8);
         HEAT_LAUNCH_UPD(64, 16, 8, false);
     }
     if (D == 128 && K <= 16) {
         if (deterministic) { if (cache) return launch_one<128, 16, 1, false, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(128, 16, 1, false); }
+        blocks = cap_blocks(c, blocks, 4);
         HEAT_LAUNCH_UPD(128, 16, 4, false);
     }
     if (D == 32 && K <= 32) {
         if (deterministic) { if (cache) return launch_one<32, 8, 1, true, UPD_STORE, true>(c, P, blocks); HEAT_LAUNCH(32, 8, 1, true); }
+        blocks = cap_blocks(c, blocks, 8);
         HEAT_LAUNCH_UPD(32, 8, 8, true);
     }
 #undef HEAT_LAUNCH_UPD
@@ -112,25 +131,14 @@ int dispatch(Ctx *c, const TrainParams &P, bool deterministic, int warps_overrid
                 "): the warp-per-sample kernel covers emb_dim 32/64 with num_negs <= 32 and emb_dim 128 with num_negs <= 16 (engine 0 or 3 covers the rest)");
 }
 
-// engine 0 (auto): the CTA kernel keeps the reference's loss / Recall with one sample in flight per ~600 item rows
-//  and spends that budget on <= #SMs samples with the shortest latency.  The warp-per-sample
-// kernel holds a sample ~5x longer between its reads and its writes, so it needs ~1100 item rows per sample in flight
-// for the same per-epoch loss tolerance (profiles/r01_recall_parity.md: at 620-630 rows per sample its Recall@20 is
-// within 0.0002 of the reference but its first epochs' losses are 0.05-0.06 above; at 1126 rows per sample -- the 2 M-item
-// shard of BASELINE configs[4] -- its epoch losses are within 0.01 of the CTA kernel's at twice the samples/s).  Once the
-// item table is large enough for a whole grid of it (#SMs x warps) that kernel is the faster parity-safe choice.
-// Returns the warps per block to run it with, 0 = stay on the CTA kernel.
-int auto_warp_engine(const Ctx *c, int D, int K)
+// engine 0 (auto), DESIGN.md section 6: the warp-per-sample kernel on its full grid with the fresh-grad update
+// (UPD_FRESH) keeps Recall@20 within 0.0035 of the reference on the three BASELINE shapes at 2.5-6x the samples/s of the
+// CTA-per-sample kernel; its per-epoch loss trails the reference's in the first epochs (thousands of samples in flight)
+// and meets it by epoch 20.  The CTA kernel (engine 2) is the strict choice: loss within 0.03 in every epoch.  Returns
+// true when the warp kernel covers (D, K) and nothing asks for the sequential order.
+bool auto_warp_engine(const Ctx *c, int D, int K)
 {
-    if (!warp_covers(D, K) || c->cfg.deterministic || c->cfg.max_blocks || c->cfg.warps_per_block || c->cfg.blocks_per_sm) return 0;
-    const uint64_t budget = c->cfg.num_items / 1100, sms = (uint64_t)c->num_sms;
-    if (D == 64 && K <= 16) {
-        if (budget >= sms * 12) return 12;
-        if (budget >= sms * 8) return 8;      // 8 warps x 148 in flight at ~8 us per sample still beats 148 CTAs at 1.5 us
-        return 0;
-    }
-    const uint64_t w = D == 128 ? 4 : 8;      // the fixed block shapes of the other instantiations
-    return budget >= sms * w ? (int)w : 0;
+    return warp_covers(D, K) && !c->cfg.deterministic;
 }
 
 }  // namespace
@@ -179,8 +187,8 @@ int run_engine(Ctx *c, const TrainParams &P)
 {
     int rc = -1;
     c->last_engine = 0;
-    const int auto_w = c->cfg.engine == 0 ? auto_warp_engine(c, (int)c->cfg.emb_dim, P.K) : 0;
-    if (auto_w) { rc = dispatch(c, P, false, auto_w); c->last_engine = 1; }
+    const bool auto_w = c->cfg.engine == 0 && auto_warp_engine(c, (int)c->cfg.emb_dim, P.K);
+    if (auto_w) { rc = dispatch(c, P, false); c->last_engine = 1; }
     else if (c->cfg.engine != 1 && c->cfg.engine != 3) { rc = dispatch_cta(c, P, c->cfg.deterministic != 0); c->last_engine = 2; }      // 0 auto, 2 forced
     if (rc == -1 && c->cfg.engine == 2) rc = fail("engine 2 (CTA per sample) does not cover this (emb_dim, num_negs)");
     if (rc == -1) {

@@ -56,9 +56,11 @@ typedef struct heat_config {
                                    aggregator at epoch end (behavior_aggregators.cpp:141-146) */
     uint32_t warps_per_block;   /* 0 = tuned default */
     uint32_t blocks_per_sm;     /* 0 = tuned default */
-    uint32_t update_mode;       /* item-row write-back in the Hogwild grid: 0 store the stepped snapshot (the
-                                   reference's sequence), 1 re-read the rows right before the step, 2 apply the
-                                   step as L2 vector reductions (no lost updates). deterministic=1 forces 0 */
+    uint32_t update_mode;       /* item-row write-back in the Hogwild grid of the warp-per-sample kernel: 0 = default = 1: the grad rows
+                                   are read right before the step and the weight rows stepped by L2 reductions (short
+                                   read-modify-write window, no lost weight step); 2: grad and weight rows both by L2
+                                   reductions; 3: the stepped snapshot is stored (the reference's own sequence; loses updates
+                                   under thousands of concurrent samples).  deterministic=1 forces 3 */
     uint32_t sync_average;      /* multi-GPU item/W0 reconciliation: 0 = default = 1: every replica becomes the MEAN of the
                                    replicas (== base + mean of the rank deltas: the fork's averaging, engine.cpp:354-375);
                                    2: base + SUM of the rank deltas.  The mean keeps Recall@20 on the one-GPU run's for every
@@ -66,13 +68,14 @@ typedef struct heat_config {
     uint32_t history_mode;      /* 0 default: the history column sums are gathered once per run of a user's
                                    consecutive samples and patched with the exact change of the rows the warp
                                    rewrites; 1: re-gathered for every sample (the reference's literal sequence) */
-    uint32_t engine;            /* 0 auto (see heat_last_engine); 1 warp-per-sample kernel (train_kernel.cuh: highest throughput, thousands of
-                                   samples in flight); 2 CTA-per-sample kernel (train_kernel_cta.cuh: lowest latency per
-                                   sample, one sample in flight per thread block -- the default where it applies) */
-    uint32_t max_blocks;        /* cap on thread blocks = bound on Hogwild concurrency.  0 = default: with engine 0 the
-                                   CTA kernel runs min(#SMs, max(8, num_items/600)) blocks (one sample in flight per
-                                   ~600 item rows keeps Recall@20 on the reference's); engines
-                                   1 and 2 use one grid over all SMs */
+    uint32_t engine;            /* 0 auto (see heat_last_engine): the warp-per-sample kernel on its full grid where it covers
+                                   (emb_dim, num_negs) -- Recall@20 within 0.005 of the reference, per-epoch loss trailing it in the
+                                   first epochs; 1 the same kernel, forced; 2 CTA-per-sample kernel
+                                   (train_kernel_cta.cuh): one sample in flight per thread block, per-epoch loss within 0.03 AND
+                                   Recall@20 within 0.005 of the reference -- the strict choice; 3 large-negative kernel */
+    uint32_t max_blocks;        /* cap on thread blocks = bound on Hogwild concurrency.  0 = default: the warp-per-sample kernel
+                                   runs one block per SM, at most one warp in flight per 16 item rows; the CTA kernel (engine 2)
+                                   min(#SMs, max(8, num_items/600)) blocks */
     uint32_t exchange_mode;     /* multi-GPU item/W0 reconciliation: 0 auto -- ONE kernel per rank that reads every rank's
                                    replica over NVLink peer memory (CUDA IPC), reduces its slice of the rows and writes
                                    the result back into every replica (comm.cu); NCCL all-reduce when peer mapping is
@@ -146,8 +149,7 @@ int heat_last_kernel_ms(heat_ctx *ctx, float *ms);
 int heat_last_epoch_ms(heat_ctx *ctx, float *ms);
 /* kernel family the last heat_train_epoch / heat_train_range ran: 1 warp-per-sample (train_kernel.cuh), 2 CTA-per-sample
  * (train_kernel_cta.cuh), 3 large-negative (train_kernel_bigk.cuh); 0 before the first launch.  With engine 0 the
- * library picks: large num_negs -> 3; an item table large enough for a full grid of warps at one sample in flight per
- * ~1100 item rows (>= 1.30 M items for 8 warps per SM, >= 1.95 M for 12, at D=64, K<=16) -> 1; otherwise 2. */
+ * library picks: deterministic -> 2 (1 where 2 does not cover the shape); large num_negs -> 3; otherwise 1. */
 int heat_last_engine(heat_ctx *ctx, int *engine);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 int heat_launch_count(heat_ctx *ctx, uint64_t *n);

@@ -1,6 +1,7 @@
 """Per-epoch loss and final Recall/NDCG of the GPU path vs the compiled reference (oracle/_ref) on the
 same seeded synthetic inputs (BASELINE configs 1-3).  Usage: recall_parity.py <shape> <epochs> [modes...]
-A mode is `warps:max_blocks:update_mode`, e.g. 12:0:0 (full grid) or 4:32:0 (128 warps in flight)."""
+A mode is `auto` (library defaults), `cta:<max_blocks>:<blocks_per_sm>` (engine 2) or `warps:max_blocks:update_mode` (engine 1;
+update_mode 0/1 fresh-grad, 2 atomic, 3 snapshot store), e.g. 12:0:0 (full grid) or 4:32:3 (128 warps in flight, store)."""
 import json
 import os
 import sys
@@ -38,8 +39,10 @@ out["reference"] = {"losses": ref_losses, "sec_per_epoch": ref_s, "threads": o.m
 print("reference", [round(x, 4) for x in ref_losses], {k: round(v, 4) for k, v in ref_res.items()}, f"{ref_s:.2f} s/epoch", flush=True)
 for mode in modes:
     t = synth.init_tables(d.num_users, d.num_items, D)
-    if mode == "auto":                    # library defaults: CTA kernel, blocks = min(#SMs, num_items/600)
+    if mode == "auto":                    # library defaults
         ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip)
+    elif mode == "strict":                # engine 2 at its default concurrency: blocks = min(#SMs, num_items/600)
+        ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=2)
     elif mode.startswith("cta"):          # cta:<max_blocks>:<blocks_per_sm>
         _, mb, bps = mode.split(":")
         ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=2, max_blocks=int(mb), blocks_per_sm=int(bps))
