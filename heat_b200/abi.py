@@ -46,7 +46,7 @@ class HeatConfig(C.Structure):
         ("chunk", C.c_uint32), ("deterministic", C.c_uint32), ("w0_tail_mode", C.c_uint32),
         ("warps_per_block", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("update_mode", C.c_uint32),
         ("sync_average", C.c_uint32), ("history_mode", C.c_uint32), ("engine", C.c_uint32), ("max_blocks", C.c_uint32),
-        ("exchange_mode", C.c_uint32), ("tile_sampler", C.c_uint32), ("sync_grads", C.c_uint32), ("reserved0", C.c_uint32),
+        ("exchange_mode", C.c_uint32), ("tile_sampler", C.c_uint32), ("sync_grads", C.c_uint32), ("eval_precision", C.c_uint32),
     ]
 
 
@@ -191,7 +191,7 @@ class Context:
     def __init__(self, emb_dim, num_negs, num_users, num_items, clip_val=1.0, l_r=1e-2, milestones=(10,),
                  l2=1e-7, seed=2022, sample_offset=0, chunk=0, deterministic=False, w0_tail_mode=0,
                  warps_per_block=0, blocks_per_sm=0, max_blocks=0, update_mode=0, sync_average=0, history_mode=0, engine=0, neg_sampler=0, tile_size=512, refresh_interval=8192,
-                 tile_sampler=0, exchange_mode=0, sync_grads=0, device=0):
+                 tile_sampler=0, exchange_mode=0, sync_grads=0, eval_precision=0, device=0):
         self._ms = np.asarray(list(milestones), dtype=np.uint64)
         cfg = HeatConfig(emb_dim=emb_dim, num_negs=num_negs, num_users=num_users, num_items=num_items,
                          train_size=0, neg_sampler=neg_sampler, tile_size=tile_size,
@@ -201,7 +201,7 @@ class Context:
                          w0_tail_mode=w0_tail_mode, warps_per_block=warps_per_block, blocks_per_sm=blocks_per_sm,
                          max_blocks=max_blocks, update_mode=update_mode,
                          sync_average=sync_average, history_mode=history_mode, engine=engine, tile_sampler=tile_sampler,
-                         exchange_mode=exchange_mode, sync_grads=sync_grads)
+                         exchange_mode=exchange_mode, sync_grads=sync_grads, eval_precision=eval_precision)
         self.D, self.K, self.U, self.I = emb_dim, num_negs, num_users, num_items
         self.N = 0
         self.H = 0

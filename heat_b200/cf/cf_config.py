@@ -13,7 +13,7 @@ except ImportError:  # run as a script from this directory, like the reference
     import cf_c
 
 GPU_KNOBS = ("seed", "sample_offset", "chunk", "deterministic", "update_mode", "warps_per_block", "max_blocks",
-             "sync_average", "sync_grads", "w0_tail_mode", "history_mode", "engine", "tile_sampler", "exchange_mode")
+             "sync_average", "sync_grads", "w0_tail_mode", "eval_precision", "history_mode", "engine", "tile_sampler", "exchange_mode")
 
 
 class CFConfig(CPPBase):

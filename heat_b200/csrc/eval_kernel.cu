@@ -24,6 +24,7 @@
 //                              the sets exchange thresholds and set 0 merges the two lists at the end
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include "heat_ctx.cuh"
@@ -48,6 +49,7 @@ struct EvalParams {
     int *topk_ids;                 // [U, k]
     float *topk_scores;            // [U, k]
     float *dense_out;              // [U, I] when k == 0
+    const int *perm;               // top-k mode: column c of the (norm-ordered) item operand is item perm[c]; null = identity
     unsigned long long *glist;     // [grid, 3, 128, 32*(sort_e-1)] sorted lists of the user block in flight (L2-resident scratch)
     int sort_e;                    // keys per lane in the fold: 4, 8 or 16
 };
@@ -63,6 +65,81 @@ __global__ void split_tf32_kernel(const float *__restrict__ src, float *__restri
         asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(x - hf));
         hi[i] = hf;
         lo[i] = __uint_as_float(l);
+    }
+}
+
+// ---- item order of the top-k mode ------------------------------------------------------------------------------
+// The streaming top-k admits every score above the row's current k-th best, so the number of candidates (and of
+// folds, which are what the epilogue's instructions go to) depends on how fast the thresholds rise: ~k ln(I/k) per row
+// when the items come in id order.  Scores are |u||i|cos, and trained item norms spread over a factor of three, so the
+// items are streamed in order of DESCENDING NORM: the thresholds are close to final after the first tenth of the
+// table and the candidate count falls by ~3x (measured on trained tables).  The result does not depend on the order
+// (keys carry the original item id).  The order is a counting sort on the top 16 bits of |i|^2 (128 buckets per
+// octave): a histogram, one scan, one scatter; the TF32 split writes the item operand in that order.
+constexpr int NORM_BINS = 1 << 16;
+__global__ void item_norm_hist_kernel(const float *__restrict__ w, int rows, int D, unsigned short *__restrict__ key, unsigned *__restrict__ hist)
+{
+    const int lane = threadIdx.x & 31;
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (int r = wid; r < rows; r += nw) {
+        float a = 0.f;
+        for (int j = lane; j < D; j += 32) { const float x = w[(size_t)r * D + j]; a = fmaf(x, x, a); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) {
+            const unsigned kb = isfinite(a) ? (__float_as_uint(a) >> 16) : 0u;     // non-negative float: bit order = value order
+            key[r] = (unsigned short)kb;
+            atomicAdd(&hist[kb], 1u);
+        }
+    }
+}
+// offs[b] = number of items in bins above b (descending order); one block of 1024 threads, 64 bins each
+__global__ void __launch_bounds__(1024) norm_scan_kernel(const unsigned *__restrict__ hist, unsigned *__restrict__ offs)
+{
+    __shared__ unsigned part[1024];
+    const int t = threadIdx.x;
+    const int top = NORM_BINS - 1 - t * 64;                  // this thread's bins: top, top-1, ..., top-63
+    unsigned sum = 0;
+    for (int j = 0; j < 64; ++j) sum += hist[top - j];
+    part[t] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {                     // inclusive scan of the per-thread totals
+        const unsigned v = t >= o ? part[t - o] : 0u;
+        __syncthreads();
+        part[t] += v;
+        __syncthreads();
+    }
+    unsigned run = part[t] - sum;
+    for (int j = 0; j < 64; ++j) { offs[top - j] = run; run += hist[top - j]; }
+}
+__global__ void norm_scatter_kernel(const unsigned short *__restrict__ key, int rows, unsigned *__restrict__ offs, int *__restrict__ perm)
+{
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x)
+        perm[atomicAdd(&offs[key[r]], 1u)] = r;
+}
+// the TF32 split of the item table, row c of the output = item perm[c]
+__global__ void split_tf32_perm_kernel(const float *__restrict__ src, const int *__restrict__ perm, float *__restrict__ hi,
+                                       float *__restrict__ lo, int rows, int D)
+{
+    const int vpr = D / 4;                                   // float4 per row
+    const size_t n4 = (size_t)rows * vpr;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i / vpr), j = (int)(i % vpr);
+        const float4 x = *reinterpret_cast<const float4 *>(src + (size_t)perm[c] * D + 4 * j);
+        float4 h, l;
+        const float xs[4] = {x.x, x.y, x.z, x.w};
+        float hs[4], ls[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            uint32_t hb, lb;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(xs[e]));
+            hs[e] = __uint_as_float(hb);
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(xs[e] - hs[e]));
+            ls[e] = __uint_as_float(lb);
+        }
+        h = make_float4(hs[0], hs[1], hs[2], hs[3]); l = make_float4(ls[0], ls[1], ls[2], ls[3]);
+        *reinterpret_cast<float4 *>(hi + i * 4) = h;
+        *reinterpret_cast<float4 *>(lo + i * 4) = l;
     }
 }
 
@@ -204,6 +281,7 @@ struct FoldHot {
     uint32_t buf_s;                             // shared-space address of the set's candidate buffers [EV_CAP][128] x 8 B
     unsigned long long *glist;                  // the set's lists of the user block in flight [128][32*(E-1)]
     const int *train_items;
+    const int *perm;                            // column -> item id (null = identity)
     unsigned long long *thr_pub;                // this set's published k-th scores [128] (or null)
     unsigned tag;                               // user block tag of the published thresholds
 };
@@ -239,16 +317,21 @@ __device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, const
         const int n = __shfl_sync(0xffffffffu, cnt, r);
         const long long tbr = __shfl_sync(0xffffffffu, tb, r);
         const int nr = __shfl_sync(0xffffffffu, ntrain, r);
-        int pos = __shfl_sync(0xffffffffu, cur, r);
+        const int pos = __shfl_sync(0xffffffffu, cur, r);        // (unused since the columns are norm-ordered: the whole list is scanned)
         unsigned long long key[E];
         unsigned long long *gl = H.glist + (size_t)row * LCAP;
 #pragma unroll
         for (int i = 0; i < LE; ++i) key[i] = ((has >> r) & 1u) ? __ldcg(gl + lane + 32 * i) : 0ull;
         const unsigned long long raw = lane < n ? lds64(H.buf_s + (uint32_t)(lane * EV_M + row) * 8u) : 0ull;   // (column, score bits)
-        const int col = lane < n ? (int)(unsigned)raw : -1;
+        // the candidate's item id (the columns are in norm order); candidates that are train items of the user are
+        // dropped: the user's sorted list is read 32 ids at a time and every lane looks its id up in the chunks whose
+        // range can hold it (5-step shuffle binary search)
+        const int col = lane < n ? (H.perm ? __ldg(H.perm + (int)(unsigned)raw) : (int)(unsigned)raw) : -1;
         bool masked = false;
-        while (pos < nr) {
+        for (int pos = 0; pos < nr; pos += 32) {
             const int tv = pos + lane < nr ? __ldg(train_items + tbr + pos + lane) : 0x7fffffff;
+            const int first = __shfl_sync(0xffffffffu, tv, 0), last = __shfl_sync(0xffffffffu, tv, 31);
+            if (!__any_sync(0xffffffffu, col >= first && col <= last)) continue;
             int lo = 0;
 #pragma unroll
             for (int s = 16; s > 0; s >>= 1) {
@@ -256,9 +339,6 @@ __device__ __forceinline__ unsigned long long topk_fold(const FoldArgs &A, const
                 if (tt < col) lo += s;
             }
             masked |= __shfl_sync(0xffffffffu, tv, lo) == col;
-            const int adv = __popc(__ballot_sync(0xffffffffu, tv < col_next));
-            pos += adv;
-            if (adv < 32) break;
         }
         key[LE] = (lane < n && !masked) ? topk_key(__uint_as_float((unsigned)(raw >> 32)), col) : 0ull;
         bitonic_sort_asc<E, LE, 1>(key, lane);
@@ -431,7 +511,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         FA.other_list = nullptr; FA.out_ids = P.topk_ids; FA.out_scores = P.topk_scores;
         FA.half_pub = thr_sh + (NSETS + set) * EV_M;
         FoldHot FH;
-        FH.k = k; FH.lane = lane; FH.row0 = q * 32; FH.buf_s = buf_s; FH.train_items = P.train_items;
+        FH.k = k; FH.lane = lane; FH.row0 = q * 32; FH.buf_s = buf_s; FH.train_items = P.train_items; FH.perm = P.perm;
         FH.thr_pub = (NSETS > 1 && k > 0) ? thr_sh + set * EV_M : nullptr;
         unsigned rbi = 0;
         for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++rbi) {
@@ -649,6 +729,8 @@ struct EvalScratch {
     double *sums = nullptr;
     float *dense = nullptr; size_t dense_elems = 0;
     unsigned long long *glist = nullptr; size_t glist_elems = 0;
+    int *perm = nullptr; unsigned short *norm_key = nullptr; size_t perm_elems = 0, key_elems = 0;   // norm order of the items (top-k mode)
+    unsigned *norm_hist = nullptr;                                                                    // [2][NORM_BINS]: histogram, offsets
 };
 
 template <class T> int ensure(T **p, size_t *have, size_t need)
@@ -667,7 +749,7 @@ EvalScratch *scratch(Ctx *c)
     return static_cast<EvalScratch *>(c->eval_scratch);
 }
 
-int split_tables(Ctx *c, EvalScratch *s)
+int split_tables(Ctx *c, EvalScratch *s, bool norm_order)
 {
     const size_t D = c->cfg.emb_dim, ue = c->cfg.num_users * D, ie = c->cfg.num_items * D;
     size_t h;
@@ -678,8 +760,21 @@ int split_tables(Ctx *c, EvalScratch *s)
     h = s->item_elems; if (int rc = ensure(&s->item_lo, &h, ie)) return rc;
     s->item_elems = ie;
     split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->user_w, s->user_hi, s->user_lo, ue);
-    split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->item_hi, s->item_lo, ie);
-    c->launches += 2;
+    if (norm_order) {
+        const int I = (int)c->cfg.num_items;
+        if (int rc = ensure(&s->perm, &s->perm_elems, (size_t)I)) return rc;
+        if (int rc = ensure(&s->norm_key, &s->key_elems, (size_t)I)) return rc;
+        if (!s->norm_hist) HEAT_CUDA(cudaMalloc(&s->norm_hist, 2 * NORM_BINS * sizeof(unsigned)));
+        HEAT_CUDA(cudaMemsetAsync(s->norm_hist, 0, NORM_BINS * sizeof(unsigned), c->stream));
+        item_norm_hist_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, I, (int)D, s->norm_key, s->norm_hist);
+        norm_scan_kernel<<<1, 1024, 0, c->stream>>>(s->norm_hist, s->norm_hist + NORM_BINS);
+        norm_scatter_kernel<<<c->num_sms * 4, 256, 0, c->stream>>>(s->norm_key, I, s->norm_hist + NORM_BINS, s->perm);
+        split_tf32_perm_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->perm, s->item_hi, s->item_lo, I, (int)D);
+        c->launches += 5;
+    } else {
+        split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->item_hi, s->item_lo, ie);
+        c->launches += 2;
+    }
     HEAT_CUDA(cudaGetLastError());
     return 0;
 }
@@ -796,9 +891,11 @@ int topk_device(Ctx *c, EvalScratch *s, uint32_t k, const int64_t *train_indptr,
     if (int rc = ensure(&s->topk_ids, &s->topk_elems, (size_t)U * k)) return rc;
     if (int rc = ensure(&s->topk_scores, &s->topk_scores_elems, (size_t)U * k)) return rc;
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
-    if (int rc = split_tables(c, s)) return rc;
+    const bool norm_order = std::getenv("HEAT_EVAL_ID_ORDER") == nullptr;     // experiment switch: stream the items in id order
+    if (int rc = split_tables(c, s, norm_order)) return rc;
     EvalParams P{};
-    P.k = (int)k; P.terms = 3;
+    P.k = (int)k; P.terms = c->cfg.eval_precision == 1 ? 1 : 3;
+    P.perm = norm_order ? s->perm : nullptr;
     P.train_indptr = train_indptr ? s->train_indptr : nullptr;
     P.train_items = train_indptr ? s->train_items : nullptr;
     P.topk_ids = s->topk_ids; P.topk_scores = s->topk_scores;
@@ -854,7 +951,7 @@ int eval_dense(Ctx *c, float *out_host)
     slab = std::min<uint64_t>(slab, (U + EV_M - 1) / EV_M * EV_M);
     if (int rc = ensure(&s->dense, &s->dense_elems, (size_t)slab * I)) return rc;
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
-    if (int rc = split_tables(c, s)) return rc;
+    if (int rc = split_tables(c, s, false)) return rc;
     for (uint64_t u0 = 0; u0 < U; u0 += slab) {
         const uint64_t n = std::min(slab, U - u0);
         EvalParams P{};
@@ -875,6 +972,7 @@ void eval_free(Ctx *c)
     cudaFree(s->user_hi); cudaFree(s->user_lo); cudaFree(s->item_hi); cudaFree(s->item_lo);
     cudaFree(s->topk_ids); cudaFree(s->topk_scores); cudaFree(s->train_indptr); cudaFree(s->train_items);
     cudaFree(s->test_indptr); cudaFree(s->test_items); cudaFree(s->sums); cudaFree(s->dense); cudaFree(s->glist);
+    cudaFree(s->perm); cudaFree(s->norm_key); cudaFree(s->norm_hist);
     delete s;
     c->eval_scratch = nullptr;
 }

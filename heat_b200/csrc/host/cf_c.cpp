@@ -53,7 +53,8 @@ PYBIND11_MODULE(cf_c, cf_module)
         .def_readwrite("tile_sampler", &CFConfig::tile_sampler)
         .def_readwrite("exchange_mode", &CFConfig::exchange_mode)
         .def_readwrite("sync_grads", &CFConfig::sync_grads)
-        .def_readwrite("w0_tail_mode", &CFConfig::w0_tail_mode);
+        .def_readwrite("w0_tail_mode", &CFConfig::w0_tail_mode)
+        .def_readwrite("eval_precision", &CFConfig::eval_precision);
 
     py::module_ datasets = m.def_submodule("datasets", "datasets");
     py::class_<Dataset, std::shared_ptr<Dataset>>(datasets, "Dataset");

@@ -71,7 +71,7 @@ Engine::Engine(std::shared_ptr<Dataset> dataset, std::shared_ptr<AggregatorWeigh
     hc.deterministic = cfg_->deterministic; hc.update_mode = cfg_->update_mode; hc.warps_per_block = cfg_->warps_per_block;
     hc.max_blocks = cfg_->max_blocks; hc.sync_average = cfg_->sync_average;
     hc.history_mode = cfg_->history_mode; hc.engine = cfg_->engine; hc.tile_sampler = cfg_->tile_sampler; hc.exchange_mode = cfg_->exchange_mode;
-    hc.sync_grads = cfg_->sync_grads; hc.w0_tail_mode = cfg_->w0_tail_mode;
+    hc.sync_grads = cfg_->sync_grads; hc.w0_tail_mode = cfg_->w0_tail_mode; hc.eval_precision = cfg_->eval_precision;
     check(heat_create(&ctx_, &hc, pick_device()), "heat_create");
     try {
         // the stored column count is the layout; datasets.py:79 sets max_his to the same number

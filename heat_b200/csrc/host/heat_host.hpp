@@ -27,7 +27,7 @@ struct CFConfig {
     // GPU-path knobs (defaults keep every existing YAML valid); settable as attributes from Python
     idx_t seed = 2022, sample_offset = 0;
     uint32_t chunk = 0, deterministic = 0, update_mode = 0, warps_per_block = 0, max_blocks = 0, sync_average = 0,
-             history_mode = 0, engine = 0, tile_sampler = 0, exchange_mode = 0, sync_grads = 0, w0_tail_mode = 0;
+             history_mode = 0, engine = 0, tile_sampler = 0, exchange_mode = 0, sync_grads = 0, w0_tail_mode = 0, eval_precision = 0;
     CFConfig(idx_t emb_dim, idx_t num_negs, idx_t num_users, idx_t num_items, idx_t train_size, idx_t neg_sampler,
              idx_t tile_size, idx_t refresh_interval, idx_t num_subepochs, val_t l2, val_t clip_val,
              const std::vector<idx_t> &milestones, val_t l_r);

@@ -239,3 +239,78 @@ def generate_powerlaw(num_users: int, num_items: int, train_size: int, max_his: 
     his[n_train == 0] = 0
     masks = h.astype(np.uint64).reshape(-1, 1)
     return ClickData(num_users, num_items, max_his, clicks, his, masks, train_indptr, train_items, test_indptr, test_items)
+
+
+def generate_powerlaw_block(block: int, users_per_block: int, num_items: int, samples_per_block: int, max_his: int = 100,
+                            seed: int = 2022, test_frac: float = 0.2, deg_a: float = 0.6, zipf_a: float = 1.0,
+                            n_clusters: int = 256, p_in: float = 0.8, max_degree: int = 4096) -> ClickData:
+    """User block `block` of ONE large power-law dataset WITH planted structure (BASELINE.json configs[4] on 8 GPUs: eight
+    blocks of 1.25 M users over one 2 M-item catalogue).  What all blocks share comes from `seed` alone -- the items'
+    clusters and popularity law -- so the union of the blocks is one dataset whatever process generates which block; a
+    block's users (power-law degrees, a cluster each, 80 % of their items drawn from that cluster by popularity) come
+    from (seed, block).  Fully vectorised.  Local user ids 0..users_per_block-1; items global."""
+    g = np.random.default_rng(seed)
+    n_clusters = max(1, min(n_clusters, num_items // 8))
+    item_cluster = g.integers(0, n_clusters, size=num_items)
+    pop = 1.0 / (g.permutation(num_items) + max(10.0, num_items / 300.0)) ** zipf_a
+    glob_cdf = np.cumsum(pop)
+    order = np.argsort(item_cluster, kind="stable")
+    clus_cdf = np.cumsum(pop[order])
+    starts = np.searchsorted(item_cluster[order], np.arange(n_clusters), side="left")
+    ends = np.searchsorted(item_cluster[order], np.arange(n_clusters), side="right")
+    lo = np.where(starts > 0, clus_cdf[np.maximum(starts, 1) - 1], 0.0)
+    hi = clus_cdf[np.maximum(ends, 1) - 1]
+
+    rng = np.random.default_rng([seed, 7919, block])
+    total = int(samples_per_block / (1.0 - test_frac))
+    raw = (rng.permutation(users_per_block) + 1.0) ** (-deg_a)
+    deg = np.clip(np.rint(raw * (total / raw.sum())).astype(np.int64), 2, max_degree)
+    user_cluster = rng.integers(0, n_clusters, size=users_per_block)
+    owner = np.repeat(np.arange(users_per_block, dtype=np.int64), deg)
+    r = rng.random(owner.size)
+    inside = rng.random(owner.size) < p_in
+    c = user_cluster[owner]
+    T = 1 << 22                                              # global draws through a quantile table (see generate_powerlaw)
+    table = np.minimum(np.searchsorted(glob_cdf, (np.arange(T) + 0.5) * (glob_cdf[-1] / T), side="right"), num_items - 1)
+    item = table[np.minimum((r * T).astype(np.int64), T - 1)]
+    idx = np.nonzero(inside & (ends[c] > starts[c]))[0]
+    ci = c[idx]
+    pos_in = np.searchsorted(clus_cdf, lo[ci] + r[idx] * (hi[ci] - lo[ci]), side="right")
+    item[idx] = order[np.clip(pos_in, starts[ci], ends[ci] - 1)]
+    key = np.sort((owner << 32) | item.astype(np.int64))
+    key = key[np.concatenate([[True], key[1:] != key[:-1]])]            # drops a user's repeated items
+    owner, item = key >> 32, (key & 0xffffffff).astype(np.int32)
+    shuffle = np.argsort((owner << 32) | rng.integers(0, 1 << 31, size=owner.size), kind="stable")   # random order inside every user
+    owner, item = owner[shuffle], item[shuffle]
+    n_u = np.bincount(owner, minlength=users_per_block).astype(np.int64)
+    indptr = np.concatenate([[0], np.cumsum(n_u)])
+    pos = np.arange(owner.size, dtype=np.int64) - indptr[owner]
+    n_train = np.minimum(np.maximum(1, np.floor(n_u * (1.0 - test_frac)).astype(np.int64)), n_u)
+    is_train = pos < n_train[owner]
+    train_items, test_items = item[is_train], item[~is_train]
+    train_indptr = np.concatenate([[0], np.cumsum(n_train)]).astype(np.int64)
+    test_indptr = np.concatenate([[0], np.cumsum(n_u - n_train)]).astype(np.int64)
+    clicks = np.empty((train_items.size, 2), dtype=np.uint64)
+    clicks[:, 0] = owner[is_train].astype(np.uint64)
+    clicks[:, 1] = train_items.astype(np.uint64)
+    j = np.minimum(np.arange(max_his, dtype=np.int64)[None, :], np.maximum(n_train, 1)[:, None] - 1)
+    his = train_items[np.minimum(train_indptr[:-1, None] + j, max(train_items.size - 1, 0))].astype(np.uint64)
+    his[n_train == 0] = 0
+    masks = np.minimum(n_train, max_his).astype(np.uint64).reshape(-1, 1)
+    # the evaluation masks need every user's train items sorted by id; the click order stays random
+    srt = np.argsort((owner[is_train] << 32) | train_items.astype(np.int64), kind="stable")
+    return ClickData(users_per_block, num_items, max_his, clicks, his, masks, train_indptr, train_items[srt], test_indptr, test_items)
+
+
+def concat_blocks(blocks) -> ClickData:
+    """The union of user blocks as one ClickData (users renumbered block after block): what one process would train."""
+    U = sum(b.num_users for b in blocks)
+    clicks, off, so, to = [], 0, 0, 0
+    tr_p, te_p = [np.zeros(1, np.int64)], [np.zeros(1, np.int64)]
+    for b in blocks:
+        c = b.clicks.copy(); c[:, 0] += np.uint64(off); clicks.append(c)
+        tr_p.append(b.train_indptr[1:] + so); te_p.append(b.test_indptr[1:] + to)
+        off += b.num_users; so += int(b.train_indptr[-1]); to += int(b.test_indptr[-1])
+    return ClickData(U, blocks[0].num_items, blocks[0].max_his, np.concatenate(clicks), np.concatenate([b.his_items for b in blocks]),
+                     np.concatenate([b.masks for b in blocks]), np.concatenate(tr_p), np.concatenate([b.train_items for b in blocks]),
+                     np.concatenate(te_p), np.concatenate([b.test_items for b in blocks]))

@@ -89,7 +89,9 @@ typedef struct heat_config {
                                    ALL ranks' touches, as one GPU training the union of the shards would; 0 = grad rows stay
                                    local to a rank.  Only matters with more than one exchange per epoch (the rows are zeroed
                                    at every epoch end) */
-    uint32_t reserved0;
+    uint32_t eval_precision;    /* fused evaluation (heat_eval_topk / heat_eval_metrics): 0 = default = 3: three TF32 passes per tile
+                                   (A_lo.B_hi + A_hi.B_lo + A_hi.B_hi: fp32-level scores, 2e-6 relative); 1: one TF32 pass (1e-3 relative
+                                   scores; the top-50 sets differ in a few near-ties).  heat_eval_dense always uses 3 */
 } heat_config;
 
 /* ---- life cycle -------------------------------------------------------------------- */

@@ -131,3 +131,40 @@ def test_full_size_amazon_shape_eval_properties():
         same = (ids[u] == want)
         assert same.mean() > 0.9 and np.allclose(sc[u], row[ids[u]], rtol=1e-5, atol=1e-7), (u, same.mean())
         assert set(ids[u].tolist()) == set(want.tolist()) or np.abs(row[ids[u]].min() - row[want].min()) < 1e-9
+
+
+def test_norm_ordered_streaming_does_not_change_the_result():
+    """The fused top-k streams the items in order of descending norm (eval_kernel.cu); ids, scores, masking and ties must
+    be those of the id-ordered definition: a table whose row norms spread over 6x, exact duplicates of rows (ties) and a
+    train mask."""
+    rng = np.random.default_rng(11)
+    U, I, D = 300, 5000, 64
+    uw = (rng.standard_normal((U, D)) * 0.1).astype(np.float32)
+    iw = (rng.standard_normal((I, D)) * 0.1).astype(np.float32) * rng.uniform(0.5, 3.0, (I, 1)).astype(np.float32)
+    iw[100:140] = iw[4000:4040]                                        # exact ties between far-apart ids
+    deg = rng.integers(0, 40, U)
+    indptr = np.concatenate([[0], np.cumsum(deg)]).astype(np.int64)
+    items = np.concatenate([np.sort(rng.choice(I, d_, replace=False)) for d_ in deg]).astype(np.int32)
+    ctx = ctx_for(uw, iw)
+    ids, sc = ctx.eval_topk(50, indptr, items)
+    ctx.close()
+    check_topk(ids, sc, uw.astype(np.float64) @ iw.astype(np.float64).T, indptr, items, 50)
+
+
+def test_single_pass_tf32_precision_knob():
+    """heat_config.eval_precision = 1: one TF32 pass instead of three.  Reported: top-50 set overlap and the change of
+    Recall@20 against the default (fp32-level) path on the reference-generated evaluation fixture."""
+    g = load_golden("eval_d64")
+    U, D = g["user_w"].shape
+    out = {}
+    for prec in (0, 1):
+        ctx = abi.Context(D, 4, U, g["item_w"].shape[0], eval_precision=prec)
+        ctx.bind_tables(g["user_w"].copy(), g["item_w"].copy(), np.zeros((D, D), np.float32))
+        ids, _ = ctx.eval_topk(50, g["train_indptr"], g["train_items"])
+        res, _ = ctx.eval_metrics(g["train_indptr"], g["train_items"], g["test_indptr"], g["test_items"])
+        ctx.close()
+        out[prec] = (ids, res)
+    overlap = np.mean([len(set(a.tolist()) & set(b.tolist())) / 50.0 for a, b in zip(out[0][0], out[1][0])])
+    d20 = out[1][1]["Recall(k=20)"] - out[0][1]["Recall(k=20)"]
+    print(f"single-pass TF32: top-50 set overlap {overlap:.4f}, dRecall@20 {d20:+.5f}")
+    assert overlap > 0.97 and abs(d20) < 3e-3
