@@ -334,6 +334,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     d2h = uw.nbytes + iw.nbytes + w0.nbytes + 8
     e2e_steps = max(3, min(args.steps, 10))
 
+    ctx.sync_to_host()                           # the host buffers hold the trained tables, as after any Engine.train_one_epoch()
+
     def e2e_step():
         ctx.set_dataset(clicks, his, masks)      # uint64 host arrays -> device int32
         ctx.upload_tables()                      # host tables -> device
@@ -520,7 +522,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--engine", type=int, default=0, help="0 auto, 1 warp-per-sample, 2 CTA-per-sample, 3 large-negative")
     ap.add_argument("--no-strict-mode", action="store_true", help="skip the extra measurement of the loss-strict CTA-per-sample engine")
-    ap.add_argument("--sync-interval", type=int, default=DEFAULT_SYNC["interval"], help="samples per GPU between exchanges of the replicated item table (0 = auto: max(65536, 3 x items))")
+    ap.add_argument("--sync-interval", type=int, default=DEFAULT_SYNC["interval"], help="samples per GPU between exchanges of the replicated item table (0 = auto: max(65536, 8 x items))")
     ap.add_argument("--sync-average", type=int, default=DEFAULT_SYNC["average"], help="0/1 mean of the replicas (the fork's averaging; default), 2 sum of the rank deltas")
     ap.add_argument("--sync-grads", type=int, default=DEFAULT_SYNC["grads"], help="1 = the persistent item grad rows are exchanged too")
     ap.add_argument("--no-convergence", action="store_true", help="N > 1: skip the Recall@20-vs-one-GPU leg")

@@ -69,9 +69,8 @@ def metrics_from_topk(top_k_items, test_indptr, test_items, metrics):
             continue
         n += 1
         hit = np.isin(top_k_items[u, :max_k], true) & (top_k_items[u, :max_k] >= 0)
-        n_true = len(set(true.tolist()))
         for j, (kind, k) in enumerate(parsed):
-            sums[j] += _one(kind, k, hit, n_true if kind != "Recall" else true.size)
+            sums[j] += _one(kind, k, hit, true.size)      # the list length, duplicates included (metrics.py:57-61,108-113; metrics_kernel)
     return dict(zip(metrics, (sums / max(n, 1)).tolist()))
 
 

@@ -71,52 +71,12 @@ __global__ void split_tf32_kernel(const float *__restrict__ src, float *__restri
 // ---- item order of the top-k mode ------------------------------------------------------------------------------
 // The streaming top-k admits every score above the row's current k-th best, so the number of candidates (and of
 // folds, which are what the epilogue's instructions go to) depends on how fast the thresholds rise: ~k ln(I/k) per row
-// when the items come in id order.  Scores are |u||i|cos, and trained item norms spread over a factor of three, so the
-// items are streamed in order of DESCENDING NORM: the thresholds are close to final after the first tenth of the
-// table and the candidate count falls by ~3x (measured on trained tables).  The result does not depend on the order
-// (keys carry the original item id).  The order is a counting sort on the top 16 bits of |i|^2 (128 buckets per
-// octave): a histogram, one scan, one scatter; the TF32 split writes the item operand in that order.
-constexpr int NORM_BINS = 1 << 16;
-__global__ void item_norm_hist_kernel(const float *__restrict__ w, int rows, int D, unsigned short *__restrict__ key, unsigned *__restrict__ hist)
-{
-    const int lane = threadIdx.x & 31;
-    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
-    for (int r = wid; r < rows; r += nw) {
-        float a = 0.f;
-        for (int j = lane; j < D; j += 32) { const float x = w[(size_t)r * D + j]; a = fmaf(x, x, a); }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-        if (lane == 0) {
-            const unsigned kb = isfinite(a) ? (__float_as_uint(a) >> 16) : 0u;     // non-negative float: bit order = value order
-            key[r] = (unsigned short)kb;
-            atomicAdd(&hist[kb], 1u);
-        }
-    }
-}
-// offs[b] = number of items in bins above b (descending order); one block of 1024 threads, 64 bins each
-__global__ void __launch_bounds__(1024) norm_scan_kernel(const unsigned *__restrict__ hist, unsigned *__restrict__ offs)
-{
-    __shared__ unsigned part[1024];
-    const int t = threadIdx.x;
-    const int top = NORM_BINS - 1 - t * 64;                  // this thread's bins: top, top-1, ..., top-63
-    unsigned sum = 0;
-    for (int j = 0; j < 64; ++j) sum += hist[top - j];
-    part[t] = sum;
-    __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1) {                     // inclusive scan of the per-thread totals
-        const unsigned v = t >= o ? part[t - o] : 0u;
-        __syncthreads();
-        part[t] += v;
-        __syncthreads();
-    }
-    unsigned run = part[t] - sum;
-    for (int j = 0; j < 64; ++j) { offs[top - j] = run; run += hist[top - j]; }
-}
-__global__ void norm_scatter_kernel(const unsigned short *__restrict__ key, int rows, unsigned *__restrict__ offs, int *__restrict__ perm)
-{
-    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x)
-        perm[atomicAdd(&offs[key[r]], 1u)] = r;
-}
+// when the items come in id order.  Popular items are near the top of most users' lists, so the items are streamed in
+// order of DESCENDING TRAIN-SET DEGREE: the thresholds are close to final after a small part of the table and the
+// candidate count falls ~3x (measured on trained tables; ordering by the items' current norms does as well on trained
+// tables but is the WORST order for barely trained ones, whose relevant items have the smaller norms).  The order is a
+// property of the train CSR: computed on the host when a CSR is uploaded, resident with it.  The result does not
+// depend on the order (keys carry the original item id); the TF32 split writes the item operand in that order.
 // the TF32 split of the item table, row c of the output = item perm[c]
 __global__ void split_tf32_perm_kernel(const float *__restrict__ src, const int *__restrict__ perm, float *__restrict__ hi,
                                        float *__restrict__ lo, int rows, int D)
@@ -729,8 +689,8 @@ struct EvalScratch {
     double *sums = nullptr;
     float *dense = nullptr; size_t dense_elems = 0;
     unsigned long long *glist = nullptr; size_t glist_elems = 0;
-    int *perm = nullptr; unsigned short *norm_key = nullptr; size_t perm_elems = 0, key_elems = 0;   // norm order of the items (top-k mode)
-    unsigned *norm_hist = nullptr;                                                                    // [2][NORM_BINS]: histogram, offsets
+    int *perm = nullptr; size_t perm_elems = 0;     // items by descending train-set degree (resident with the train CSR; top-k mode)
+    bool perm_ok = false;
 };
 
 template <class T> int ensure(T **p, size_t *have, size_t need)
@@ -749,7 +709,7 @@ EvalScratch *scratch(Ctx *c)
     return static_cast<EvalScratch *>(c->eval_scratch);
 }
 
-int split_tables(Ctx *c, EvalScratch *s, bool norm_order)
+int split_tables(Ctx *c, EvalScratch *s, bool norm_order /* item operand in s->perm order */)
 {
     const size_t D = c->cfg.emb_dim, ue = c->cfg.num_users * D, ie = c->cfg.num_items * D;
     size_t h;
@@ -761,16 +721,8 @@ int split_tables(Ctx *c, EvalScratch *s, bool norm_order)
     s->item_elems = ie;
     split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->user_w, s->user_hi, s->user_lo, ue);
     if (norm_order) {
-        const int I = (int)c->cfg.num_items;
-        if (int rc = ensure(&s->perm, &s->perm_elems, (size_t)I)) return rc;
-        if (int rc = ensure(&s->norm_key, &s->key_elems, (size_t)I)) return rc;
-        if (!s->norm_hist) HEAT_CUDA(cudaMalloc(&s->norm_hist, 2 * NORM_BINS * sizeof(unsigned)));
-        HEAT_CUDA(cudaMemsetAsync(s->norm_hist, 0, NORM_BINS * sizeof(unsigned), c->stream));
-        item_norm_hist_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, I, (int)D, s->norm_key, s->norm_hist);
-        norm_scan_kernel<<<1, 1024, 0, c->stream>>>(s->norm_hist, s->norm_hist + NORM_BINS);
-        norm_scatter_kernel<<<c->num_sms * 4, 256, 0, c->stream>>>(s->norm_key, I, s->norm_hist + NORM_BINS, s->perm);
-        split_tf32_perm_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->perm, s->item_hi, s->item_lo, I, (int)D);
-        c->launches += 5;
+        split_tf32_perm_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->perm, s->item_hi, s->item_lo, (int)c->cfg.num_items, (int)D);
+        c->launches += 2;
     } else {
         split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->item_hi, s->item_lo, ie);
         c->launches += 2;
@@ -886,12 +838,30 @@ int topk_device(Ctx *c, EvalScratch *s, uint32_t k, const int64_t *train_indptr,
     const uint64_t U = c->cfg.num_users;
     if (train_indptr) {
         if (!train_items) return fail("train_items is null");
+        const uint64_t fp_before = s->train_fp;
         if (int rc = upload_csr(c, train_indptr, train_items, U, &s->train_indptr, &s->indptr_n, &s->train_items, &s->train_n, true, &s->train_fp)) return rc;
+        if (s->train_fp != fp_before || !s->perm_ok) {            // a new train CSR: its popularity order
+            const size_t I = c->cfg.num_items, nnz = (size_t)train_indptr[U];
+            std::vector<uint32_t> deg(I, 0);
+            for (size_t i = 0; i < nnz; ++i) {
+                if ((uint32_t)train_items[i] >= I) return fail("train_items: id out of range");
+                deg[train_items[i]] += 1;
+            }
+            std::vector<int> perm(I);
+            for (size_t i = 0; i < I; ++i) perm[i] = (int)i;
+            std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return deg[a] > deg[b]; });
+            s->perm_ok = false;
+            if (int rc = ensure(&s->perm, &s->perm_elems, I)) return rc;
+            HEAT_CUDA(cudaMemcpyAsync(s->perm, perm.data(), I * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+            HEAT_CUDA(cudaStreamSynchronize(c->stream));          // `perm` is a host temporary
+            s->perm_ok = true;
+        }
     }
     if (int rc = ensure(&s->topk_ids, &s->topk_elems, (size_t)U * k)) return rc;
     if (int rc = ensure(&s->topk_scores, &s->topk_scores_elems, (size_t)U * k)) return rc;
     HEAT_CUDA(cudaEventRecord(c->ev0, c->stream));
-    const bool norm_order = std::getenv("HEAT_EVAL_ID_ORDER") == nullptr;     // experiment switch: stream the items in id order
+    // items in popularity order when a train CSR came with the call (HEAT_EVAL_ID_ORDER: experiment switch, id order)
+    const bool norm_order = train_indptr && s->perm_ok && std::getenv("HEAT_EVAL_ID_ORDER") == nullptr;
     if (int rc = split_tables(c, s, norm_order)) return rc;
     EvalParams P{};
     P.k = (int)k; P.terms = c->cfg.eval_precision == 1 ? 1 : 3;
@@ -972,7 +942,7 @@ void eval_free(Ctx *c)
     cudaFree(s->user_hi); cudaFree(s->user_lo); cudaFree(s->item_hi); cudaFree(s->item_lo);
     cudaFree(s->topk_ids); cudaFree(s->topk_scores); cudaFree(s->train_indptr); cudaFree(s->train_items);
     cudaFree(s->test_indptr); cudaFree(s->test_items); cudaFree(s->sums); cudaFree(s->dense); cudaFree(s->glist);
-    cudaFree(s->perm); cudaFree(s->norm_key); cudaFree(s->norm_hist);
+    cudaFree(s->perm);
     delete s;
     c->eval_scratch = nullptr;
 }

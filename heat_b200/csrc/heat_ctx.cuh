@@ -78,7 +78,7 @@ int fail(const std::string &msg);
 inline bool sync_mean(const Ctx *c) { return c->cfg.sync_average != 2; }
 inline uint64_t sync_interval_of(const Ctx *c)
 {
-    return c->sync_interval ? c->sync_interval : std::max<uint64_t>(65536, 3 * c->cfg.num_items);
+    return c->sync_interval ? c->sync_interval : std::max<uint64_t>(65536, 8 * c->cfg.num_items);
 }
 
 // hot-tile sampler fields of a kernel parameter block from the config (tile_sampler && neg_sampler == 1), else uniform

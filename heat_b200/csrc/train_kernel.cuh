@@ -40,6 +40,8 @@ struct TrainParams {
     unsigned long long sample_offset, seed;
     unsigned epoch;
     int max_his, num_items, K, chunk, drop_w0_tail;
+    long long tail_begin;    // guided scheduling: [begin, tail_begin) is handed out in chunks of `chunk` samples, [tail_begin, end)
+    int tail_chunk;          // in chunks of `tail_chunk` (small): the warps / CTAs of a launch finish within a few samples of each other
     int upd;                 // item-row update mode, see UPD_* below
     int no_cache;            // 1: gather the history rows for every sample (history_mode 1)
     int cache_rows;          // train_kernel_bigk.cuh: negative rows kept in shared memory between the two passes
@@ -49,6 +51,20 @@ struct TrainParams {
 };
 
 constexpr unsigned FULL = 0xffffffffu;
+
+// chunk number c of a launch -> its sample range (false: no such chunk).  Chunks are consecutive ranges in file order.
+__device__ __forceinline__ bool chunk_range(const TrainParams &P, long long c, long long &s0, long long &s1)
+{
+    const long long nb = (P.tail_begin - P.begin + P.chunk - 1) / P.chunk;
+    if (c < nb) {
+        s0 = P.begin + c * P.chunk;
+        s1 = min(P.tail_begin, s0 + (long long)P.chunk);
+        return true;
+    }
+    s0 = P.tail_begin + (c - nb) * P.tail_chunk;
+    s1 = min(P.end, s0 + (long long)P.tail_chunk);
+    return s0 < P.end;
+}
 
 // How a sample's item rows (positive + negatives: weight row and persistent grad row) are written back.
 //   UPD_STORE  the reference's own sequence (matrix_factorization.cpp:133-149,169-174): the row
@@ -243,8 +259,6 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
     const float score_mul = (float)(1.0 / 0.07);     // matrix_factorization.cpp:101
     const int K = P.K;
     double loss_acc = 0.0;
-    const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
-
     // CACHE: state carried across the consecutive samples of one user (a "run").  The history column
     // sums are gathered once per run and then patched with the exact change of every history row this
     // warp itself rewrites; the user's weight and grad rows stay in registers.  In file order with one
@@ -260,9 +274,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) train_kernel(const TrainParams 
         unsigned long long c = 0;
         if (lane == 0) c = atomicAdd(P.chunk_counter, 1ULL);
         c = __shfl_sync(FULL, c, 0);
-        if ((long long)c >= nchunks) break;
-        const long long s0 = P.begin + (long long)c * P.chunk;
-        const long long s1 = min(P.end, s0 + (long long)P.chunk);
+        long long s0, s1;
+        if (!chunk_range(P, (long long)c, s0, s1)) break;
 
         for (long long s = s0; s < s1; ++s) {
             __syncwarp();   // rows written by other lanes for the previous sample are visible

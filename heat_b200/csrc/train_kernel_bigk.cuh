@@ -130,7 +130,6 @@ __global__ void __launch_bounds__(BigKCfg<D>::NT, 1) train_bigk_kernel(const Tra
     const int col = tid / RQ, rb = tid % RQ;                 // W0 column, row block
     const float gamma = 0.4f, omg = 1.0f - gamma;
     const float score_mul = (float)(1.0 / 0.07);
-    const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
     constexpr int TILE = G * UNR;
     const int ntile = (K + TILE - 1) / TILE;
 
@@ -177,8 +176,8 @@ __global__ void __launch_bounds__(BigKCfg<D>::NT, 1) train_bigk_kernel(const Tra
         if (tid == 0) *sh_chunk = atomicAdd(P.chunk_counter, 1ULL);
         __syncthreads();
         const long long ch = (long long)*sh_chunk;
-        if (ch >= nchunks) break;
-        const long long s0 = P.begin + ch * P.chunk, s1 = min(P.end, s0 + (long long)P.chunk);
+        long long s0, s1;
+        if (!chunk_range(P, ch, s0, s1)) break;
         for (long long s = s0; s < s1; ++s) {
             const int2 click = __ldg(&P.clicks[s]);
             const int u = click.x, p = click.y;

@@ -122,19 +122,18 @@ template <int NPS> struct CtaCtrl {
 // (fetches the next chunk when the current one is used up; cnt = 0 when there is none).
 template <int D, int NPS, bool TILE>
 __device__ __forceinline__ void cta_prepare_batch(const TrainParams &P, CtaBatch<NPS> *B, int lane, CtaCtrl<NPS> &c,
-                                                  long long nchunks, bool no_cache)
+                                                  bool no_cache)
 {
     constexpr int KM = 16 * NPS;
     if (c.s >= c.s_end) {                                  // next chunk (warp-uniform)
         unsigned long long ch = 0;
         if (lane == 0) ch = atomicAdd(P.chunk_counter, 1ULL);
         ch = __shfl_sync(FULL, ch, 0);
-        if ((long long)ch >= nchunks) {
+        if (!chunk_range(P, (long long)ch, c.s, c.s_end)) {
+            c.s = c.s_end = 0;
             if (lane == 0) B->cnt = 0;
             return;
         }
-        c.s = P.begin + (long long)ch * P.chunk;
-        c.s_end = min(P.end, c.s + (long long)P.chunk);
         c.chunk_begin = c.s;
         c.carry_u = -1;
     }
@@ -248,7 +247,6 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int role = tid < C::NEGT ? 0 : tid < C::USR0 ? 1 : tid < C::GMV0 ? 2 : tid < C::CTRL0 ? 4 : 3;   // warp-uniform
-    const long long nchunks = (P.end - P.begin + P.chunk - 1) / P.chunk;
     const bool no_cache = P.no_cache != 0;
 
     // ======== control warp: its own loop, two batches ahead of the row warps ========
@@ -259,7 +257,7 @@ __global__ void __launch_bounds__(CtaCfg<D, NPS>::NT, 1) train_cta_kernel(const 
                 if (lane == 0) ring[slot_].cnt = 0;
                 return false;
             }
-            cta_prepare_batch<D, NPS, TILE>(P, &ring[slot_], lane, ctl, nchunks, no_cache);
+            cta_prepare_batch<D, NPS, TILE>(P, &ring[slot_], lane, ctl, no_cache);
             __syncwarp();
             return ring[slot_].cnt != 0;
         };

@@ -175,6 +175,11 @@ TrainParams make_params(Ctx *c, uint64_t begin, uint64_t end, unsigned long long
     P.epoch = (unsigned)c->epoch;
     P.max_his = (int)c->max_his; P.num_items = (int)c->cfg.num_items; P.K = (int)c->cfg.num_negs;
     P.chunk = (int)c->cfg.chunk;
+    // guided scheduling: the last part of the range goes out in chunks of 8, so that the launch does not end with every
+    // warp somewhere inside a 64-sample chunk (a sync segment of a multi-GPU epoch is only ~150 samples per warp)
+    P.tail_chunk = std::min(8, P.chunk);
+    P.tail_begin = (long long)end - (long long)std::min<uint64_t>((end - begin) / 3, 57344);
+    if (c->cfg.deterministic) P.tail_begin = (long long)end;
     P.drop_w0_tail = (int)c->cfg.w0_tail_mode;
     P.upd = (int)c->cfg.update_mode;
     P.lr = c->l_r; P.lr_w0 = c->cfg.l_r * exp_lr_w0_scale(); P.clip = c->cfg.clip_val;

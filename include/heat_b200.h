@@ -219,9 +219,10 @@ int heat_comm_init(heat_ctx *ctx, int rank, int world, const uint8_t unique_id[1
  * (engine.cpp:148-152,262-286,354-375): one all-reduce of the item-table delta and one of
  * the W0 delta since the last sync; every rank ends with base + sum of deltas. */
 int heat_comm_sync_items(heat_ctx *ctx);
-/* samples a rank trains between two exchanges.  0 (the initial value) = auto: max(65536, 3 x num_items) -- every item row
- * is touched ~50 times per replica between exchanges, 10 exchanges per epoch at the Amazon-Books shape; any value >= the
- * shard size = once per epoch.  Every rank must set the same value. */
+/* samples a rank trains between two exchanges.  0 (the initial value) = auto: max(65536, 8 x num_items) -- every item row
+ * is touched ~140 times per replica between exchanges, 4 exchanges per epoch at the Amazon-Books shape (Recall@20 does not
+ * move between 3 and 74 exchanges per epoch, one per epoch is too few: DESIGN.md section 7); any value >= the shard size =
+ * once per epoch.  Every rank must set the same value. */
 int heat_set_sync_interval(heat_ctx *ctx, uint64_t samples);
 /* exchanges of the last heat_train_epoch and their total device time (CUDA events on the context's stream), ms */
 int heat_last_exchange(heat_ctx *ctx, uint64_t *count, float *ms);

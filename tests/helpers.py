@@ -15,7 +15,9 @@ def load_golden(name):
 
 
 def rel_err(a, b):
-    """max |a-b| relative to the largest reference magnitude (the north-star's 1e-5 bar)."""
+    """max |a-b| relative to the LARGEST reference magnitude: a max-norm ratio, not an element-wise relative error
+    (near-zero elements of a table would make the latter meaningless); the north-star's "1e-5 relative" is read in
+    this norm."""
     denom = max(float(np.abs(b).max()), 1e-12)
     return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / denom
 

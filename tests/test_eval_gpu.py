@@ -133,8 +133,8 @@ def test_full_size_amazon_shape_eval_properties():
         assert set(ids[u].tolist()) == set(want.tolist()) or np.abs(row[ids[u]].min() - row[want].min()) < 1e-9
 
 
-def test_norm_ordered_streaming_does_not_change_the_result():
-    """The fused top-k streams the items in order of descending norm (eval_kernel.cu); ids, scores, masking and ties must
+def test_popularity_ordered_streaming_does_not_change_the_result():
+    """The fused top-k streams the items in order of descending train-set degree (eval_kernel.cu); ids, scores, masking and ties must
     be those of the id-ordered definition: a table whose row norms spread over 6x, exact duplicates of rows (ties) and a
     train mask."""
     rng = np.random.default_rng(11)

@@ -68,7 +68,7 @@ def test_c_oracle_w0_update_matches_golden_when_tables_frozen():
         assert abs(l1 - l2) < 1e-4 * max(1.0, abs(l2))
     assert not np.array_equal(a[2], g["init_w0"])          # W0 did move
     assert rel_err(a[2], b[2]) < 1e-5
-    assert np.array_equal(a[0], b[0]) is False or True      # user rows are overwritten with the aggregate
+    assert not np.array_equal(a[0], g["init_user_w"])     # user rows are overwritten with the aggregate even at lr 0
     assert rel_err(a[0], b[0]) < 1e-5 and rel_err(a[1], b[1]) < 1e-5
 
 

@@ -8,7 +8,7 @@ evaluation (score GEMM / top-k with the seven metric sums all-reduced).
 Rank r generates and trains user block r of ONE structured power-law dataset (heat_b200.synth.generate_powerlaw_block:
 shared item clusters and popularity law, 1.25 M users and ~60 M samples per block at --scale 1), against its replica of
 the 2 M-item table; the replicas are reconciled by the library's default exchange (mean of the replicas every
-max(65536, 3 x items) samples, one kernel per rank over NVLink peer memory).  One JSON line (rank 0): per-rank and
+max(65536, 8 x items) samples, one kernel per rank over NVLink peer memory).  One JSON line (rank 0): per-rank and
 total samples/s, exchanges and their share of the epoch, evaluation ms, Recall, and the size-independent parity
 properties (sampler slice bit-exact with the host twin, finite decreasing loss, top-k rows equal to an fp64 host
 recomputation on sampled users).  --scale S divides users, items and samples by S; with --reference (small scales) rank 0
