@@ -33,10 +33,19 @@
 namespace heat {
 namespace {
 
+#ifdef HEAT_EVAL_STATS
+// development counters (-DHEAT_EVAL_STATS through HEAT_NVCC_DEFS): [0] candidates appended, [1] row folds, [2] score groups with a
+// survivor somewhere in the warp, [3] score groups
+__device__ unsigned long long g_eval_stats[4];
+#define EV_STAT(i, n) atomicAdd(&g_eval_stats[i], (unsigned long long)(n))
+#else
+#define EV_STAT(i, n) do { } while (0)
+#endif
+
 constexpr int EV_M = 128;          // users per CTA block = TMEM lanes
 constexpr int EV_CAP = 30;         // candidate-buffer entries per (epilogue set, user row): <= 32 (one key per lane in the fold);
                                    // 30 leaves room for a third B stage at D = 64
-constexpr int ACC_STAGES = 4;      // TMEM accumulator ring
+constexpr int ACC_STAGES = 8;      // TMEM accumulator ring (8 x 64 columns = all 512: a set whose warp is folding has four tiles of slack)
 constexpr int MAX_B_STAGES = 4;
 
 struct EvalParams {
@@ -364,7 +373,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
 {
     using S = EvalSmem<D, NT>;
     constexpr int KA = S::KA;
-    constexpr uint32_t TMEM_COLS = ACC_STAGES * NT;          // 256 (NT=64) or 128 (NT=32)
+    constexpr uint32_t TMEM_COLS = ACC_STAGES * NT;          // 512 (NT=64) or 256 (NT=32)
     constexpr uint32_t IDESC = ptx::idesc_tf32(EV_M, NT);
 
     extern __shared__ uint8_t smem_raw[];
@@ -402,7 +411,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         if (lane == 0) {
             uint32_t it_b = 0, it_a = 0;
             for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++it_a) {
-                ptx::mbar_wait(a_empty, (it_a & 1) ^ 1);
+                HEAT_MBAR_WAIT(a_empty, (it_a & 1) ^ 1);
                 ptx::mbar_expect_tx(a_full, (terms == 3 ? 2 : 1) * KA * S::A_ATOM);
                 for (int a = 0; a < KA; ++a) {
                     ptx::tma_load_2d(sA + a * S::A_ATOM, &tmA_hi, a_full, a * 32, rb * EV_M);
@@ -410,7 +419,7 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                 }
                 for (int t = 0; t < P.n_item_tiles; ++t, ++it_b) {
                     const int s = it_b % P.b_stages;
-                    ptx::mbar_wait(&empty[s], ((it_b / P.b_stages) & 1) ^ 1);
+                    HEAT_MBAR_WAIT(&empty[s], ((it_b / P.b_stages) & 1) ^ 1);
                     ptx::mbar_expect_tx(&full[s], (terms == 3 ? 2 : 1) * KA * S::B_ATOM);
                     uint8_t *dst = sB + (size_t)s * S::B_STAGE;
                     for (int a = 0; a < KA; ++a) {
@@ -422,29 +431,38 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
-        if (lane == 0) {
+        {   // the whole warp walks the tile loop (converged); one elected lane issues the MMAs and the commits
             uint32_t it_b = 0, it_acc = 0, it_a = 0;
-            const uint32_t a_addr = ptx::smem_u32(sA);
+            // Descriptors: ONE thread issues every MMA, so its instruction count per tile is on the critical path (24 MMAs
+            // per 128x64 tile; building both descriptors from scratch for each made this thread, not the tensor pipe or
+            // the epilogue, the limiter: ~35 dependent integer instructions per MMA).  The start-address field is
+            // (addr >> 4) in the low 14 bits and every operand lies below 256 KiB, so desc(base + off) = desc(base) + (off >> 4):
+            // one base descriptor per operand, compile-time offsets in fully unrolled loops.
+            const uint64_t a_desc0 = ptx::smem_desc_k_sw128(ptx::smem_u32(sA));
+            const uint64_t b_desc00 = ptx::smem_desc_k_sw128(ptx::smem_u32(sB));
             for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++it_a) {
-                ptx::mbar_wait(a_full, it_a & 1);
+                HEAT_MBAR_WAIT(a_full, it_a & 1);
                 for (int t = 0; t < P.n_item_tiles; ++t, ++it_b, ++it_acc) {
                     const int s = it_b % P.b_stages, acc = it_acc % ACC_STAGES;
-                    ptx::mbar_wait(&tempty[acc], ((it_acc / ACC_STAGES) & 1) ^ 1);
-                    ptx::mbar_wait(&full[s], (it_b / P.b_stages) & 1);
+                    HEAT_MBAR_WAIT(&tempty[acc], ((it_acc / ACC_STAGES) & 1) ^ 1);
+                    HEAT_MBAR_WAIT(&full[s], (it_b / P.b_stages) & 1);
                     ptx::tc_fence_after();
-                    const uint32_t b_addr = ptx::smem_u32(sB + (size_t)s * S::B_STAGE);
+                    const uint64_t b_desc0 = b_desc00 + (uint64_t)(((uint32_t)s * (uint32_t)S::B_STAGE) >> 4);
                     const uint32_t d_tmem = tmem_base + acc * NT;
+                    if (ptx::elect_one()) {
                     uint32_t accumulate = 0;
                     // small terms first: A_lo.B_hi, A_hi.B_lo, then A_hi.B_hi
-                    for (int term = (terms == 3 ? 0 : 2); term < 3; ++term) {
+#pragma unroll
+                    for (int term = 0; term < 3; ++term) {
+                        if (terms != 3 && term < 2) continue;
                         const uint32_t a_off = (term == 0 ? KA : 0) * S::A_ATOM;
                         const uint32_t b_off = (term == 1 ? KA : 0) * S::B_ATOM;
 #pragma unroll
                         for (int a = 0; a < KA; ++a) {
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk) {      // 4 x (K = 8 tf32 = 32 bytes) per 128-byte atom
-                                const uint64_t da = ptx::smem_desc_k_sw128(a_addr + a_off + a * S::A_ATOM + kk * 32);
-                                const uint64_t db = ptx::smem_desc_k_sw128(b_addr + b_off + a * S::B_ATOM + kk * 32);
+                                const uint64_t da = a_desc0 + (uint64_t)((a_off + a * S::A_ATOM + kk * 32) >> 4);
+                                const uint64_t db = b_desc0 + (uint64_t)((b_off + a * S::B_ATOM + kk * 32) >> 4);
                                 ptx::mma_tf32(d_tmem, da, db, IDESC, accumulate);
                                 accumulate = 1;
                             }
@@ -452,8 +470,11 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                     }
                     ptx::mma_commit(&empty[s]);       // B stage free once these MMAs have read it
                     ptx::mma_commit(&tfull[acc]);     // accumulator ready for the epilogue
+                    }
+                    __syncwarp();
                 }
-                ptx::mma_commit(a_empty);             // A block free for the next user block
+                if (ptx::elect_one()) ptx::mma_commit(a_empty);             // A block free for the next user block
+                __syncwarp();
             }
         }
     } else {
@@ -521,7 +542,9 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                 for (int h = 0; h < 4; ++h)
                     m4[h] = fmaxf(fmaxf(v[4 * h], v[4 * h + 1]), fmaxf(v[4 * h + 2], v[4 * h + 3]));
                 const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+                if (lane == 0) EV_STAT(3, 1);
                 if (!__any_sync(0xffffffffu, m > thr)) return;
+                if (lane == 0) EV_STAT(2, 1);
 #pragma unroll
                 for (int h = 0; h < 4; ++h) {
                     if (m4[h] > thr) {
@@ -531,19 +554,20 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
                                 sts32(wptr, (uint32_t)(colg + 4 * h + e));
                                 sts32(wptr + 4, __float_as_uint(v[4 * h + e]));
                                 wptr += EV_M * 8;
+                                EV_STAT(0, 1);
                             }
                         }
                     }
                     // a row folds as soon as its buffer may not take four more candidates
                     const unsigned over = __ballot_sync(0xffffffffu, wptr > my_s + (EV_CAP - 4) * EV_M * 8);
-                    if (over) fold(over, colg + 4 * h + 4, FOLD_STREAM);
+                    if (over) { if (lane == 0) EV_STAT(1, __popc(over)); fold(over, colg + 4 * h + 4, FOLD_STREAM); }
                 }
             };
 
             for (int t = (int)((it0 + set) & (NSETS - 1)); t < P.n_item_tiles; t += NSETS) {
                 const uint32_t it_acc = it0 + t;
                 const int acc = it_acc % ACC_STAGES;
-                ptx::mbar_wait(&tfull[acc], (it_acc / ACC_STAGES) & 1);
+                HEAT_MBAR_WAIT(&tfull[acc], (it_acc / ACC_STAGES) & 1);
                 ptx::tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * NT;
                 const int col0 = t * NT;
@@ -875,6 +899,15 @@ int topk_device(Ctx *c, EvalScratch *s, uint32_t k, const int64_t *train_indptr,
 }
 
 }  // namespace
+
+#ifdef HEAT_EVAL_STATS
+extern "C" void heat_debug_eval_stats(unsigned long long out[4], int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_eval_stats, sizeof(unsigned long long) * 4);
+    if (reset) { unsigned long long z[4] = {0, 0, 0, 0}; cudaMemcpyToSymbol(g_eval_stats, z, sizeof(z)); }
+}
+#endif
 
 int eval_topk(Ctx *c, uint32_t k, const int64_t *train_indptr, const int32_t *train_items, int32_t *ids_host, float *scores_host)
 {

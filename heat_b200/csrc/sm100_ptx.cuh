@@ -40,6 +40,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         : "memory");
 }
 
+// The same wait as a macro: the asm is attributed to the CALLING line, so that an ncu source view tells the wait sites apart
+// (producer on `empty`, MMA issuer on `tempty` / `full`, epilogue on `tfull`, ...).
+#define HEAT_MBAR_WAIT(bar, parity)                                                                                       \
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n@p bra DONE_%=;\n"   \
+                 "bra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(::heat::ptx::smem_u32(bar)), "r"((uint32_t)(parity)), "r"(0x989680u) : "memory")
+
+// one lane of a CONVERGED warp (elect.sync): the form ptxas recognises for single-thread tcgen05 issue
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
+
 // ---- TMA -----------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap *m)
 {
