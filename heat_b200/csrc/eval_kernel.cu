@@ -45,7 +45,7 @@ __device__ unsigned long long g_eval_stats[4];
 constexpr int EV_M = 128;          // users per CTA block = TMEM lanes
 constexpr int EV_CAP = 30;         // candidate-buffer entries per (epilogue set, user row): <= 32 (one key per lane in the fold);
                                    // 30 leaves room for a third B stage at D = 64
-constexpr int ACC_STAGES = 8;      // TMEM accumulator ring (8 x 64 columns = all 512: a set whose warp is folding has four tiles of slack)
+constexpr int ACC_STAGES = 4;      // TMEM accumulator ring: at most 4 tiles (fewer where 4 x NT + the 2*D columns of the A operand exceed 512)
 constexpr int MAX_B_STAGES = 4;
 
 struct EvalParams {
@@ -58,6 +58,7 @@ struct EvalParams {
     int *topk_ids;                 // [U, k]
     float *topk_scores;            // [U, k]
     float *dense_out;              // [U, I] when k == 0
+    const float *user_w;           // [U, D] fp32 rows of this launch's users (the A operand is split and written to TMEM in the kernel)
     const int *perm;               // top-k mode: column c of the (norm-ordered) item operand is item perm[c]; null = identity
     unsigned long long *glist;     // [grid, 3, 128, 32*(sort_e-1)] sorted lists of the user block in flight (L2-resident scratch)
     int sort_e;                    // keys per lane in the fold: 4, 8 or 16
@@ -115,9 +116,9 @@ __global__ void split_tf32_perm_kernel(const float *__restrict__ src, const int 
 template <int D, int NT>
 struct EvalSmem {
     static constexpr int KA = D / 32;                       // 128-byte swizzle atoms along K
-    static constexpr int A_ATOM = EV_M * 128;               // bytes of one [128 rows x 32 floats] atom
+    static constexpr int ACC = (512 - 2 * D) / NT < ACC_STAGES ? (512 - 2 * D) / NT : ACC_STAGES;   // accumulator tiles in TMEM
     static constexpr int B_ATOM = NT * 128;
-    static constexpr int A_BYTES = 2 * KA * A_ATOM;         // hi + lo
+    static constexpr int A_BYTES = 0;                       // the A operand (users) lives in tensor memory
     static constexpr int B_STAGE = 2 * KA * B_ATOM;         // hi + lo
     static constexpr int BAR_BYTES = 256;
     static constexpr int NSETS = D >= 128 ? 1 : 2;          // epilogue warp sets (D = 128: shared memory holds one buffer set)
@@ -368,18 +369,19 @@ __device__ __noinline__ unsigned long long topk_fold_dispatch(const FoldArgs &A,
 
 template <int D, int NT>
 __global__ void __launch_bounds__((EvalSmem<D, NT>::THREADS), 1)
-eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
-            const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo, const EvalParams P)
+eval_kernel(const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo, const EvalParams P)
 {
     using S = EvalSmem<D, NT>;
     constexpr int KA = S::KA;
-    constexpr uint32_t TMEM_COLS = ACC_STAGES * NT;          // 512 (NT=64) or 256 (NT=32)
+    constexpr int ACC = S::ACC;
+    constexpr uint32_t A_COL0 = ACC * NT;                    // A_hi at columns [A_COL0, A_COL0 + D), A_lo behind it
+    constexpr uint32_t TMEM_COLS = 512;                      // accumulator ring (256 / 128 columns) + A (2*D <= 256)
+    static_assert(ACC >= 2 && ACC * NT + 2 * D <= 512, "tensor memory: accumulators + the A operand");
     constexpr uint32_t IDESC = ptx::idesc_tf32(EV_M, NT);
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t *sA = smem;                                       // [hi|lo][KA][128 x 128B]
-    uint8_t *sB = sA + S::A_BYTES;                            // [stage][hi|lo][KA][NT x 128B]
+    uint8_t *sB = smem;                                       // [stage][hi|lo][KA][NT x 128B]
     constexpr int NSETS = S::NSETS;
     unsigned long long *buf = reinterpret_cast<unsigned long long *>(sB + (size_t)P.b_stages * S::B_STAGE);   // [set][EV_CAP][128] candidate keys
     unsigned long long *thr_sh = buf + (size_t)NSETS * EV_CAP * EV_M;                                          // [k-th | ceil(k/2)-th][set][128] (user block tag, score)
@@ -393,10 +395,10 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
     const int terms = P.terms;
 
     if (warp == 0 && lane == 0) {
-        ptx::prefetch_tmap(&tmA_hi); ptx::prefetch_tmap(&tmA_lo); ptx::prefetch_tmap(&tmB_hi); ptx::prefetch_tmap(&tmB_lo);
+        ptx::prefetch_tmap(&tmB_hi); ptx::prefetch_tmap(&tmB_lo);
         for (int s = 0; s < MAX_B_STAGES; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
-        for (int s = 0; s < ACC_STAGES; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4); }
-        ptx::mbar_init(a_full, 1); ptx::mbar_init(a_empty, 1);
+        for (int s = 0; s < ACC; ++s) { ptx::mbar_init(&tfull[s], 1); ptx::mbar_init(&tempty[s], 4); }
+        ptx::mbar_init(a_full, 4); ptx::mbar_init(a_empty, 1);       // a_full: the four warps of epilogue set 0 have written A
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -411,12 +413,6 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         if (lane == 0) {
             uint32_t it_b = 0, it_a = 0;
             for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++it_a) {
-                HEAT_MBAR_WAIT(a_empty, (it_a & 1) ^ 1);
-                ptx::mbar_expect_tx(a_full, (terms == 3 ? 2 : 1) * KA * S::A_ATOM);
-                for (int a = 0; a < KA; ++a) {
-                    ptx::tma_load_2d(sA + a * S::A_ATOM, &tmA_hi, a_full, a * 32, rb * EV_M);
-                    if (terms == 3) ptx::tma_load_2d(sA + (KA + a) * S::A_ATOM, &tmA_lo, a_full, a * 32, rb * EV_M);
-                }
                 for (int t = 0; t < P.n_item_tiles; ++t, ++it_b) {
                     const int s = it_b % P.b_stages;
                     HEAT_MBAR_WAIT(&empty[s], ((it_b / P.b_stages) & 1) ^ 1);
@@ -438,13 +434,13 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
             // the epilogue, the limiter: ~35 dependent integer instructions per MMA).  The start-address field is
             // (addr >> 4) in the low 14 bits and every operand lies below 256 KiB, so desc(base + off) = desc(base) + (off >> 4):
             // one base descriptor per operand, compile-time offsets in fully unrolled loops.
-            const uint64_t a_desc0 = ptx::smem_desc_k_sw128(ptx::smem_u32(sA));
+            const uint32_t a_tmem0 = tmem_base + A_COL0;      // A_hi; A_lo at + D
             const uint64_t b_desc00 = ptx::smem_desc_k_sw128(ptx::smem_u32(sB));
             for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++it_a) {
                 HEAT_MBAR_WAIT(a_full, it_a & 1);
                 for (int t = 0; t < P.n_item_tiles; ++t, ++it_b, ++it_acc) {
-                    const int s = it_b % P.b_stages, acc = it_acc % ACC_STAGES;
-                    HEAT_MBAR_WAIT(&tempty[acc], ((it_acc / ACC_STAGES) & 1) ^ 1);
+                    const int s = it_b % P.b_stages, acc = it_acc % ACC;
+                    HEAT_MBAR_WAIT(&tempty[acc], ((it_acc / ACC) & 1) ^ 1);
                     HEAT_MBAR_WAIT(&full[s], (it_b / P.b_stages) & 1);
                     ptx::tc_fence_after();
                     const uint64_t b_desc0 = b_desc00 + (uint64_t)(((uint32_t)s * (uint32_t)S::B_STAGE) >> 4);
@@ -455,15 +451,14 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
 #pragma unroll
                     for (int term = 0; term < 3; ++term) {
                         if (terms != 3 && term < 2) continue;
-                        const uint32_t a_off = (term == 0 ? KA : 0) * S::A_ATOM;
+                        const uint32_t a_off = term == 0 ? D : 0;               // columns: lo behind hi
                         const uint32_t b_off = (term == 1 ? KA : 0) * S::B_ATOM;
 #pragma unroll
                         for (int a = 0; a < KA; ++a) {
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk) {      // 4 x (K = 8 tf32 = 32 bytes) per 128-byte atom
-                                const uint64_t da = a_desc0 + (uint64_t)((a_off + a * S::A_ATOM + kk * 32) >> 4);
                                 const uint64_t db = b_desc0 + (uint64_t)((b_off + a * S::B_ATOM + kk * 32) >> 4);
-                                ptx::mma_tf32(d_tmem, da, db, IDESC, accumulate);
+                                ptx::mma_tf32_ts(d_tmem, a_tmem0 + a_off + a * 32 + kk * 8, db, IDESC, accumulate);
                                 accumulate = 1;
                             }
                         }
@@ -498,6 +493,36 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
         for (int rb = blockIdx.x; rb < P.n_row_blocks; rb += gridDim.x, ++rbi) {
             const int u = rb * EV_M + row;
             const bool row_ok = u < P.U;
+            // ---- the A operand of this user block: set 0's four warps (one per TMEM lane quadrant) split their rows into
+            //      tf32 hi / lo and write them into tensor memory -- lane = user row, one element per column.  The MMAs then
+            //      read A from TMEM: with both operands in shared memory every K=8 step re-read 4 KB of A next to 2 KB of B,
+            //      and that operand traffic, not the tensor pipe, paced the kernel.
+            if (set == 0) {
+                HEAT_MBAR_WAIT(a_empty, (rbi & 1) ^ 1);                        // the previous block's MMAs have read A
+                ptx::tc_fence_after();
+                const float *urow = P.user_w + (size_t)(row_ok ? u : 0) * D;
+                const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + A_COL0;
+#pragma unroll 1
+                for (int c0 = 0; c0 < D; c0 += 32) {
+                    uint32_t hi[32], lo[32];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 x = row_ok ? __ldg(reinterpret_cast<const float4 *>(urow + c0 + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi[j + e]) : "f"(xs[e]));
+                            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo[j + e]) : "f"(xs[e] - __uint_as_float(hi[j + e])));
+                        }
+                    }
+                    ptx::tmem_st32(ta + c0, hi);
+                    ptx::tmem_st32(ta + D + c0, lo);
+                }
+                ptx::tmem_st_wait();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(a_full);
+            }
             float thr = row_ok ? -INFINITY : INFINITY;
             uint32_t wptr = my_s;
             long long tb = 0;
@@ -566,8 +591,8 @@ eval_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ 
 
             for (int t = (int)((it0 + set) & (NSETS - 1)); t < P.n_item_tiles; t += NSETS) {
                 const uint32_t it_acc = it0 + t;
-                const int acc = it_acc % ACC_STAGES;
-                HEAT_MBAR_WAIT(&tfull[acc], (it_acc / ACC_STAGES) & 1);
+                const int acc = it_acc % ACC;
+                HEAT_MBAR_WAIT(&tfull[acc], (it_acc / ACC) & 1);
                 ptx::tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * NT;
                 const int col0 = t * NT;
@@ -703,8 +728,8 @@ int make_table_map(CUtensorMap *m, const float *base, uint64_t rows, int D, int 
 }
 
 struct EvalScratch {
-    float *user_hi = nullptr, *user_lo = nullptr, *item_hi = nullptr, *item_lo = nullptr;
-    size_t user_elems = 0, item_elems = 0;
+    float *item_hi = nullptr, *item_lo = nullptr;
+    size_t item_elems = 0;
     int *topk_ids = nullptr; float *topk_scores = nullptr; size_t topk_elems = 0;
     long long *train_indptr = nullptr; int *train_items = nullptr; size_t train_n = 0, indptr_n = 0;
     long long *test_indptr = nullptr; int *test_items = nullptr; size_t test_n = 0, test_indptr_n = 0;
@@ -735,21 +760,17 @@ EvalScratch *scratch(Ctx *c)
 
 int split_tables(Ctx *c, EvalScratch *s, bool norm_order /* item operand in s->perm order */)
 {
-    const size_t D = c->cfg.emb_dim, ue = c->cfg.num_users * D, ie = c->cfg.num_items * D;
+    const size_t D = c->cfg.emb_dim, ie = c->cfg.num_items * D;
     size_t h;
-    h = s->user_elems; if (int rc = ensure(&s->user_hi, &h, ue)) return rc;
-    h = s->user_elems; if (int rc = ensure(&s->user_lo, &h, ue)) return rc;
-    s->user_elems = ue;
     h = s->item_elems; if (int rc = ensure(&s->item_hi, &h, ie)) return rc;
     h = s->item_elems; if (int rc = ensure(&s->item_lo, &h, ie)) return rc;
     s->item_elems = ie;
-    split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->user_w, s->user_hi, s->user_lo, ue);
     if (norm_order) {
         split_tf32_perm_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->perm, s->item_hi, s->item_lo, (int)c->cfg.num_items, (int)D);
-        c->launches += 2;
+        c->launches += 1;
     } else {
         split_tf32_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->item_w, s->item_hi, s->item_lo, ie);
-        c->launches += 2;
+        c->launches += 1;
     }
     HEAT_CUDA(cudaGetLastError());
     return 0;
@@ -759,9 +780,8 @@ template <int D, int NT>
 int launch_eval(Ctx *c, EvalScratch *s, uint64_t u_begin, uint64_t u_count, EvalParams P)
 {
     using S = EvalSmem<D, NT>;
-    CUtensorMap mA_hi, mA_lo, mB_hi, mB_lo;
-    if (int rc = make_table_map(&mA_hi, s->user_hi + u_begin * D, u_count, D, EV_M)) return rc;
-    if (int rc = make_table_map(&mA_lo, s->user_lo + u_begin * D, u_count, D, EV_M)) return rc;
+    CUtensorMap mB_hi, mB_lo;
+    P.user_w = c->user_w + u_begin * D;
     if (int rc = make_table_map(&mB_hi, s->item_hi, c->cfg.num_items, D, NT)) return rc;
     if (int rc = make_table_map(&mB_lo, s->item_lo, c->cfg.num_items, D, NT)) return rc;
     int dev_smem = 0;
@@ -788,7 +808,7 @@ int launch_eval(Ctx *c, EvalScratch *s, uint64_t u_begin, uint64_t u_count, Eval
         s->glist_elems = have;
         P.glist = s->glist;
     }
-    kern<<<grid, S::THREADS, smem, c->stream>>>(mA_hi, mA_lo, mB_hi, mB_lo, P);
+    kern<<<grid, S::THREADS, smem, c->stream>>>(mB_hi, mB_lo, P);
     c->launches += 1;
     HEAT_CUDA(cudaGetLastError());
     return 0;
@@ -797,9 +817,11 @@ int launch_eval(Ctx *c, EvalScratch *s, uint64_t u_begin, uint64_t u_count, Eval
 int dispatch_eval(Ctx *c, EvalScratch *s, uint64_t u_begin, uint64_t u_count, const EvalParams &P)
 {
     switch (c->cfg.emb_dim) {
-    case 32: return launch_eval<32, 64>(c, s, u_begin, u_count, P);
-    case 64: return launch_eval<64, 64>(c, s, u_begin, u_count, P);
-    case 128: return launch_eval<128, 32>(c, s, u_begin, u_count, P);
+    // item tiles of 128: tcgen05.mma kind::tf32 runs at 59-65 % of its peak with N = 64 and at 99 % with N = 128
+    // (heat_probe_tf32_peak variants, profiles/r02_tf32_mma_shapes.md); D = 128 keeps 64 (two B stages of 64 KB)
+    case 32: return launch_eval<32, 128>(c, s, u_begin, u_count, P);
+    case 64: return launch_eval<64, 128>(c, s, u_begin, u_count, P);
+    case 128: return launch_eval<128, 64>(c, s, u_begin, u_count, P);
     default: return fail("evaluation kernel supports emb_dim 32, 64 and 128");
     }
 }
@@ -972,7 +994,7 @@ void eval_free(Ctx *c)
 {
     EvalScratch *s = static_cast<EvalScratch *>(c->eval_scratch);
     if (!s) return;
-    cudaFree(s->user_hi); cudaFree(s->user_lo); cudaFree(s->item_hi); cudaFree(s->item_lo);
+    cudaFree(s->item_hi); cudaFree(s->item_lo);
     cudaFree(s->topk_ids); cudaFree(s->topk_scores); cudaFree(s->train_indptr); cudaFree(s->train_items);
     cudaFree(s->test_indptr); cudaFree(s->test_items); cudaFree(s->sums); cudaFree(s->dense); cudaFree(s->glist);
     cudaFree(s->perm);

@@ -7,23 +7,26 @@
 // stream the evaluation kernel uses (cta_group::1, operands in shared memory), not a vendor number.
 #include "heat_ctx.cuh"
 #include "sm100_ptx.cuh"
+#include <cstdlib>
+#include <string>
 
 namespace heat {
 namespace {
 
-constexpr int PM = 128, PN = 256;
+constexpr int PM = 128, PN_MAX = 256;
 constexpr uint32_t P_TMEM_COLS = 512;
 
+template <int PN, bool A_TMEM>
 __global__ void __launch_bounds__(128, 1) tf32_peak_kernel(int iters, unsigned *timeouts)
 {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     float *sA = reinterpret_cast<float *>(smem);                       // [128 rows][32 tf32]  16 KB
-    float *sB = reinterpret_cast<float *>(smem + PM * 128);            // [256 rows][32 tf32]  32 KB
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem + (PM + PN) * 128);
+    float *sB = reinterpret_cast<float *>(smem + PM * 128);            // [PN rows][32 tf32]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem + (PM + PN_MAX) * 128);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar + 1);
 
-    for (int i = threadIdx.x; i < (PM + PN) * 32; i += blockDim.x) {
+    for (int i = threadIdx.x; i < (PM + PN_MAX) * 32; i += blockDim.x) {
         unsigned h = (unsigned)i * 2654435761u + blockIdx.x;
         h ^= h >> 15; h *= 0x2c1b3c6du; h ^= h >> 12;
         sA[i] = __uint_as_float(0x3f000000u | (h & 0x007fe000u)) - 0.75f;      // [-0.25, 0.25), already tf32-representable
@@ -43,8 +46,8 @@ __global__ void __launch_bounds__(128, 1) tf32_peak_kernel(int iters, unsigned *
             for (int acc = 0; acc < 2; ++acc)
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk)
-                    ptx::mma_tf32(tmem + acc * PN, ptx::smem_desc_k_sw128(a + kk * 32), ptx::smem_desc_k_sw128(b + kk * 32), IDESC,
-                                  (it | kk) != 0);
+                    if (A_TMEM) ptx::mma_tf32_ts(tmem + acc * PN, tmem + 2 * PN_MAX - 64 + kk * 8, ptx::smem_desc_k_sw128(b + kk * 32), IDESC, (it | kk) != 0);
+                    else ptx::mma_tf32(tmem + acc * PN, ptx::smem_desc_k_sw128(a + kk * 32), ptx::smem_desc_k_sw128(b + kk * 32), IDESC, (it | kk) != 0);
         }
         ptx::mma_commit(bar);
         // bounded wait: a probe must never hang the GPU
@@ -64,7 +67,22 @@ __global__ void __launch_bounds__(128, 1) tf32_peak_kernel(int iters, unsigned *
 
 }  // namespace
 
+template <int PN, bool A_TMEM> int probe_tf32_variant(int device, int iters, double *tflops);
+
 int probe_tf32(int device, int iters, double *tflops)
+{
+    if (const char *e = std::getenv("HEAT_PROBE_TF32_VARIANT")) {      // experiment: N = 64 / 128 / 256, A from TMEM (suffix t)
+        const std::string v(e);
+        if (v == "64") return probe_tf32_variant<64, false>(device, iters, tflops);
+        if (v == "128") return probe_tf32_variant<128, false>(device, iters, tflops);
+        if (v == "64t") return probe_tf32_variant<64, true>(device, iters, tflops);
+        if (v == "128t") return probe_tf32_variant<128, true>(device, iters, tflops);
+        if (v == "256t") return probe_tf32_variant<224, true>(device, iters, tflops);
+    }
+    return probe_tf32_variant<256, false>(device, iters, tflops);
+}
+
+template <int PN, bool A_TMEM> int probe_tf32_variant(int device, int iters, double *tflops)
 {
     if (!tflops) return fail("heat_probe_tf32_peak: null argument");
     HEAT_CUDA(cudaSetDevice(device));
@@ -75,15 +93,16 @@ int probe_tf32(int device, int iters, double *tflops)
     unsigned *timeouts = nullptr;
     HEAT_CUDA(cudaMalloc(&timeouts, sizeof(unsigned)));
     HEAT_CUDA(cudaMemset(timeouts, 0, sizeof(unsigned)));
-    const size_t smem = 1024 + (PM + PN) * 128 + 64;
-    HEAT_CUDA(cudaFuncSetAttribute(tf32_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = 1024 + (PM + PN_MAX) * 128 + 64;
+    auto kern = tf32_peak_kernel<PN, A_TMEM>;
+    HEAT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaEvent_t e0, e1;
     HEAT_CUDA(cudaEventCreate(&e0)); HEAT_CUDA(cudaEventCreate(&e1));
     double best = 0.0;
     int rc = 0;
     for (int rep = 0; rep < 4 && !rc; ++rep) {
         cudaEventRecord(e0);
-        tf32_peak_kernel<<<prop.multiProcessorCount, 128, smem>>>(iters, timeouts);
+        kern<<<prop.multiProcessorCount, 128, smem>>>(iters, timeouts);
         cudaEventRecord(e1);
         cudaError_t e = cudaEventSynchronize(e1);
         if (e != cudaSuccess) { rc = fail(std::string("heat_probe_tf32_peak: ") + cudaGetErrorString(e)); break; }
