@@ -455,8 +455,10 @@ def run_gpu_arm(args, rank, world, local_rank):
     achieved = alg / (k_ms * 1e-3) / 1e9
     table_bytes = 2 * (d.num_users + d.num_items) * D * 4
     kernel = {1: "heat::train_kernel", 2: "heat::train_cta_kernel", 3: "heat::train_bigk_kernel"}.get(engine_ran, "?")
-    cap = {2: "r01_train_cta_kernel_ncu_raw.csv", 1: "r02_train_kernel_ncu_raw.csv", 3: "r01_bigk_kernel_ncu_raw.csv"}.get(engine_ran)
-    traffic = args.ncu_traffic if args.ncu_traffic is not None else (ncu_traffic(cap) if cap and args.workload in ("amazon-book", "cfg4") else None)
+    # DRAM bytes of one launch of this kernel on this workload, from the committed ncu --set full captures
+    cap = {("amazon-book", 1): "r02_train_kernel_ncu_raw.csv", ("amazon-book", 2): "r01_train_cta_kernel_ncu_raw.csv",
+           ("cfg5-shard", 1): "r02_cfg5_shard_train_kernel_ncu_raw.csv"}.get((args.workload, engine_ran))
+    traffic = args.ncu_traffic if args.ncu_traffic is not None else (ncu_traffic(cap) if cap and world == 1 else None)
     roofline = {"kernel": kernel, "kernel_ms": k_ms, "launches_per_step": max(1, int(xch_n)) if world > 1 else 1,
                 "algorithmic_bytes_per_step": alg, "achieved": achieved, "unit": "GB/s",
                 "traffic": traffic,

@@ -216,6 +216,8 @@ int launch_train(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_host, fl
     if (loss_per_sample_host) HEAT_CUDA(cudaMalloc(&d_loss_out, (end - begin) * sizeof(float)));
     cudaError_t e = cudaMemsetAsync(c->chunk_counter, 0, sizeof(unsigned long long), c->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(c->loss_sum, 0, sizeof(double), c->stream);
+    // a slot the kernel failed to write reads back as NaN, not as whatever the allocation held
+    if (e == cudaSuccess && d_loss_out) e = cudaMemsetAsync(d_loss_out, 0xFF, (end - begin) * sizeof(float), c->stream);
     if (e != cudaSuccess) { cudaFree(d_loss_out); return fail(std::string("training launch: ") + cudaGetErrorString(e)); }
 
     const TrainParams P = make_params(c, begin, end, c->chunk_counter, c->loss_sum, d_loss_out);
@@ -298,6 +300,7 @@ int launch_train_noalloc(Ctx *c, uint64_t begin, uint64_t end, double *loss_sum_
     // the array keeps the previous call's contents: the counter and the sum must start at zero (the loss slots are all
     // written by the kernel before they are read back)
     HEAT_CUDA(cudaMemsetAsync(scratch, 0, 16, c->stream));
+    if (loss_out) HEAT_CUDA(cudaMemsetAsync(loss_out, 0xFF, (end - begin) * sizeof(float), c->stream));   // unwritten slot = NaN
 
     const TrainParams P = make_params(c, begin, end, counter, loss_sum, loss_out);
     if (int rc = run_engine(c, P)) return rc;

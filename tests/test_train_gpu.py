@@ -365,3 +365,23 @@ def test_update_modes_agree_when_nothing_races(update_mode):
     o.close()
     for g_, w_ in zip(got, want):
         assert abs(g_ - w_) / w_ < 0.05, (update_mode, got, want)
+
+
+@pytest.mark.parametrize("engine,kw", [(0, {}), (1, dict(update_mode=3)), (2, {}), (2, dict(max_blocks=3)), (3, {})])
+@pytest.mark.parametrize("lo,hi", [(0, 60000), (17, 18), (5, 70), (1000, 9001), (123, 58000)])
+def test_every_sample_of_a_range_is_processed_exactly_once(engine, kw, lo, hi):
+    """Guided scheduling (chunk_range: chunks of 64, then a tail in chunks of 8): whatever the range, every sample's loss
+    slot is written once and the launch's loss is their sum -- on the Hogwild grid of all three kernel families."""
+    d = synth.generate_named("small")
+    D, K = 64, 16
+    t = synth.init_tables(d.num_users, d.num_items, D)
+    ctx = abi.Context(D, K, d.num_users, d.num_items, engine=engine, **kw)
+    ctx.set_dataset(d.clicks, d.his_items, d.masks); ctx.bind_tables(*t)
+    sentinel = np.float32(-7.0)
+    out = np.full(hi - lo, sentinel, np.float32)
+    import ctypes as C
+    loss = C.c_double()
+    abi._ck(abi.lib().heat_train_range(ctx._h, lo, hi, C.byref(loss), out.ctypes.data_as(C.POINTER(C.c_float))))
+    ctx.close()
+    assert (out > 0).all() and np.isfinite(out).all(), int((out == sentinel).sum())
+    assert abs(float(out.astype(np.float64).sum()) - loss.value) <= 1e-3 * max(1.0, abs(loss.value))
