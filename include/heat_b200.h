@@ -74,7 +74,7 @@ typedef struct heat_config {
                                    (train_kernel_cta.cuh): one sample in flight per thread block, per-epoch loss within 0.03 AND
                                    Recall@20 within 0.005 of the reference -- the strict choice; 3 large-negative kernel */
     uint32_t max_blocks;        /* cap on thread blocks = bound on Hogwild concurrency.  0 = default: the warp-per-sample kernel
-                                   runs one block per SM, at most one warp in flight per 16 item rows; the CTA kernel (engine 2)
+                                   runs one block per SM, at most one warp in flight per 32 item rows; the CTA kernel (engine 2)
                                    min(#SMs, max(8, num_items/600)) blocks */
     uint32_t exchange_mode;     /* multi-GPU item/W0 reconciliation: 0 auto -- ONE kernel per rank that reads every rank's
                                    replica over NVLink peer memory (CUDA IPC), reduces its slice of the rows and writes

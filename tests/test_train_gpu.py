@@ -339,7 +339,7 @@ def test_auto_engine_choice():
         return e
 
     assert engine_for(40000) == 1
-    assert engine_for(300) == 1                            # a toy table: the default caps the warps in flight at one per 16 rows
+    assert engine_for(300) == 1                            # a toy table: the default caps the warps in flight at one per 32 rows
     assert engine_for(40000, max_blocks=32) == 1
     assert engine_for(40000, engine=2) == 2
     assert engine_for(40000, deterministic=True) == 2
