@@ -1,6 +1,8 @@
-"""World-size-2 CPU test (gloo) of the multi-GPU host logic: user-range sharding, the Philox
-counter base that makes negatives independent of the rank count, and the delta reconciliation
-formula that heat_comm_sync_items implements with NCCL."""
+"""World-size-2 CPU test (gloo) of the multi-GPU HOST logic: user-range sharding, the Philox counter base that makes
+negatives independent of the rank count, and the two reconciliation formulas (mean of the replicas = the default, sum
+of the rank deltas) restated in heat_b200/shard.py.  It pins the formulas and the sharding, not comm.cu: the exchange
+kernel itself is tested on GPUs by tests/test_multigpu_gpu.py (bit-identical to the NCCL path and to the single-device
+emulation group, replicas identical, 2-rank convergence against one GPU)."""
 import os
 import socket
 
@@ -50,6 +52,10 @@ def _worker(rank, port, out):
     dist.all_gather(gathered, torch.from_numpy(my_iw))
     want = shard.reconcile(iw, [g.numpy() for g in gathered])
     assert np.allclose(merged, want, rtol=0, atol=1e-7)
+    # the default rule: every replica becomes the mean of the replicas == base + mean of the deltas
+    mean = torch.from_numpy(my_iw.copy())
+    dist.all_reduce(mean)
+    assert np.allclose(mean.numpy() / WORLD, shard.reconcile(iw, [g.numpy() for g in gathered], average=True), rtol=0, atol=1e-7)
     tot = torch.tensor([loss * local.train_size, float(local.train_size)], dtype=torch.float64)
     dist.all_reduce(tot)                                     # engine.cpp:380-383
     if rank == 0:
