@@ -250,17 +250,20 @@ __global__ void __launch_bounds__(256) peer_sync_kernel(const PeerSync S)
 int peer_setup(Ctx *c, NcclApi *api)
 {
     if (c->world > MAX_PEERS || c->cfg.exchange_mode == 1 || !api->AllGather) return 0;
-    HEAT_CUDA(cudaMalloc(&c->xflags, 2 * MAX_PEERS * sizeof(unsigned long long)));
-    HEAT_CUDA(cudaMemset(c->xflags, 0, 2 * MAX_PEERS * sizeof(unsigned long long)));
-    HEAT_CUDA(cudaMalloc(&c->grid_sync, 2 * sizeof(unsigned)));
-    HEAT_CUDA(cudaMemset(c->grid_sync, 0, 2 * sizeof(unsigned)));
+    // A local failure must not return before the collectives below (the other ranks would wait in them for ever): it is
+    // recorded in mine.ok and vetoes the fused path for every rank through the agreement all-reduce.
+    bool local_ok = cudaMalloc(&c->xflags, 2 * MAX_PEERS * sizeof(unsigned long long)) == cudaSuccess &&
+                    cudaMemset(c->xflags, 0, 2 * MAX_PEERS * sizeof(unsigned long long)) == cudaSuccess &&
+                    cudaMalloc(&c->grid_sync, 2 * sizeof(unsigned)) == cudaSuccess &&
+                    cudaMemset(c->grid_sync, 0, 2 * sizeof(unsigned)) == cudaSuccess;
+    if (!local_ok) cudaGetLastError();
     constexpr int NH = 7;
     struct Export { cudaIpcMemHandle_t h[NH]; int ok; int pad[15]; };
     Export mine{};
     void *ptrs[NH] = {c->item_w, c->item_base, c->w0, c->w0_base, c->xflags, c->item_g, c->item_g_base};
     const int nh = c->item_g_base ? NH : 5;        // the grad rows travel only with sync_grads
-    mine.ok = 1;
-    for (int i = 0; i < nh; ++i)
+    mine.ok = local_ok ? 1 : 0;
+    for (int i = 0; i < nh && local_ok; ++i)
         if (cudaIpcGetMemHandle(&mine.h[i], ptrs[i]) != cudaSuccess) { mine.ok = 0; cudaGetLastError(); }
     Export *d_all = nullptr;
     HEAT_CUDA(cudaMalloc(&d_all, sizeof(Export) * c->world));

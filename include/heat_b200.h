@@ -51,9 +51,10 @@ typedef struct heat_config {
     uint32_t chunk;             /* samples a warp takes per scheduling step; default 64
                                    (the reference's omp schedule(dynamic,512), engine.cpp:327) */
     uint32_t deterministic;     /* 1: one warp walks the samples in file order (== 1 OpenMP thread) */
-    uint32_t w0_tail_mode;      /* 0 default: per-warp W0 grads left over at launch end are applied
-                                   (scaled 1/32); 1: dropped like the reference's per-thread
-                                   aggregator at epoch end (behavior_aggregators.cpp:141-146) */
+    uint32_t w0_tail_mode;      /* 0 default: W0 grads left over in a thread block's ring at launch end (< 32 samples) are
+                                   applied (scaled 1/32); 1: dropped like the reference's per-thread aggregator at epoch
+                                   end (behavior_aggregators.cpp:141-146).  A multi-GPU epoch is several launches (one per
+                                   sync segment), so the leftover is flushed (or dropped) once per segment and block */
     uint32_t warps_per_block;   /* 0 = tuned default */
     uint32_t blocks_per_sm;     /* 0 = tuned default */
     uint32_t update_mode;       /* item-row write-back in the Hogwild grid of the warp-per-sample kernel: 0 = default = 1: the grad rows
