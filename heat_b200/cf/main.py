@@ -6,8 +6,9 @@ Same YAML keys and epoch / evaluation schedule.  Differences, all on the GPU-pat
     its contiguous user range itself (the reference pickles shards from rank 0, main.py:55-69);
   * evaluation runs fused on the GPU (Engine.evaluate_metrics) and honours the YAML `metrics`
     list; `--dense-eval` takes the reference's route (evaluate0 + numpy metrics) instead;
-  * optional `gpu:` section of the YAML (seed, update_mode, max_blocks, warps_per_block,
-    sync_interval, sync_average, history_mode, engine); absent = defaults.
+  * optional `gpu:` section of the YAML (seed, engine, update_mode, max_blocks, warps_per_block, history_mode,
+    w0_tail_mode, eval_precision, sync_interval, sync_average, sync_grads, ...); absent = the library defaults
+    (engine 0; ranks reconciled by the mean of the replicas every max(65536, 8 x items) samples).
 """
 import argparse
 import os
