@@ -8,7 +8,8 @@ Reference arm = oracle/_ref (the unmodified reference sources compiled in place)
 the C restatement that is pinned to it (tests/test_oracle.py); all host threads; `sampler=2`, so both arms draw the same
 Philox negatives.  The reference is a Hogwild program whose result moves with its thread schedule, so its own run-to-run
 spread is MEASURED here (REF_RUNS runs per shape) and the stated tolerances are
-    |Recall@20 - mean reference Recall@20| <= 0.005 + reference spread (max - min)     (north_star: 0.005 absolute; both engines)
+    |mean GPU Recall@20 - mean reference Recall@20| <= 0.005 + reference spread + GPU spread (max - min over GPU_RUNS runs)
+        (north_star: 0.005 absolute; both engines; both arms are Hogwild programs whose result moves by ~0.002 run to run)
     |loss_e - mean reference loss_e| <= LOSS_TOL + reference spread of that epoch, every epoch, where LOSS_TOL is
         0.03 for engine 2, and for the default engine 0.15 in the first epoch and 0.06 afterwards: with ~1 800 samples
         in flight the loss trails the reference's early on (+0.06...+0.13 in epoch 0, measured) and meets it by epoch 20
@@ -26,6 +27,7 @@ pytestmark = pytest.mark.gpu
 
 D, K = 64, 16
 RECALL_TOL = 0.005
+GPU_RUNS = 3
 LOSS_TOL = {2: (0.03, 0.03), 0: (0.15, 0.06)}         # engine -> (first epoch, later epochs)
 THREADS = os.cpu_count() or 1
 # shape, epochs (BASELINE.json configs[0..2]), clip_val of the shape's YAML, reference runs (spread)
@@ -76,25 +78,33 @@ def test_epoch_losses_and_recall_match_the_reference_backend(name, epochs, clip,
     loss_mean, loss_spread = ref_losses.mean(0), ref_losses.max(0) - ref_losses.min(0)
     r_mean, r_spread = float(np.mean(ref_recall)), float(np.max(ref_recall) - np.min(ref_recall))
 
-    t = synth.init_tables(d.num_users, d.num_items, D)
-    ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=engine)       # engine 0 = library defaults
-    ctx.set_dataset(d.clicks, d.his_items, d.masks)
-    ctx.bind_tables(*t)
-    losses = [ctx.train_epoch() for _ in range(epochs)]
-    ran = ctx.last_engine()
-    assert ran == (1 if engine == 0 else 2)
-    ctx.sync_to_host()
-    ctx.close()
-    res = _evaluate(d, t)
+    # the GPU arm is a Hogwild program too: GPU_RUNS runs, their mean against the reference's mean, their spread added
+    runs = []
+    for _ in range(GPU_RUNS):
+        t = synth.init_tables(d.num_users, d.num_items, D)
+        ctx = abi.Context(D, K, d.num_users, d.num_items, clip_val=clip, engine=engine)       # engine 0 = library defaults
+        ctx.set_dataset(d.clicks, d.his_items, d.masks)
+        ctx.bind_tables(*t)
+        run_losses = [ctx.train_epoch() for _ in range(epochs)]
+        ran = ctx.last_engine()
+        assert ran == (1 if engine == 0 else 2)
+        ctx.sync_to_host()
+        ctx.close()
+        runs.append((run_losses, _evaluate(d, t)))
+    losses = np.mean([r[0] for r in runs], axis=0)
+    g20 = [r[1]["Recall(k=20)"] for r in runs]
+    g50 = [r[1]["Recall(k=50)"] for r in runs]
+    res = {"Recall(k=20)": float(np.mean(g20)), "Recall(k=50)": float(np.mean(g50))}
+    g_spread = float(np.max(g20) - np.min(g20))
     print(f"{name}: reference ({kind}, {THREADS} threads, {ref_runs} runs) loss {np.round(loss_mean, 4).tolist()} "
           f"spread {np.round(loss_spread, 4).tolist()} Recall@20 {r_mean:.4f} (spread {r_spread:.4f}) Recall@50 {np.mean(ref_recall50):.4f} | "
-          f"GPU engine {engine} (kernel family {ran}) loss {np.round(losses, 4).tolist()} Recall@20 {res['Recall(k=20)']:.4f} "
-          f"({res['Recall(k=20)'] - r_mean:+.4f}) Recall@50 {res['Recall(k=50)']:.4f}")
+          f"GPU engine {engine} (kernel family {ran}, {GPU_RUNS} runs) loss {np.round(losses, 4).tolist()} Recall@20 {res['Recall(k=20)']:.4f} "
+          f"({res['Recall(k=20)'] - r_mean:+.4f}, spread {g_spread:.4f}) Recall@50 {res['Recall(k=50)']:.4f}")
     for e in range(epochs):
         tol = LOSS_TOL[engine][0 if e == 0 else 1]
         assert abs(losses[e] - loss_mean[e]) <= tol + loss_spread[e], (e, losses[e], loss_mean[e], loss_spread[e])
-    assert abs(res["Recall(k=20)"] - r_mean) <= RECALL_TOL + r_spread, (res["Recall(k=20)"], r_mean, r_spread)
-    assert abs(res["Recall(k=50)"] - float(np.mean(ref_recall50))) <= 2 * RECALL_TOL + float(np.max(ref_recall50) - np.min(ref_recall50))
+    assert abs(res["Recall(k=20)"] - r_mean) <= RECALL_TOL + r_spread + g_spread, (res["Recall(k=20)"], r_mean, r_spread, g_spread)
+    assert abs(res["Recall(k=50)"] - float(np.mean(ref_recall50))) <= 2 * RECALL_TOL + float(np.max(ref_recall50) - np.min(ref_recall50)) + float(np.max(g50) - np.min(g50))
 
 
 def test_recall_of_reference_tables_agrees_with_the_reference_metric_code():
