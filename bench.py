@@ -353,6 +353,23 @@ def run_gpu_arm(args, rank, world, local_rank):
     e2e_s = reduce(time.perf_counter() - t0)
     e2e_value = n_total * e2e_steps / e2e_s
 
+    # the same with the dataset handed over ONCE (what the drop-in Engine does: ClickDataset at construction,
+    # init_modules.cpp:45-61; heat_set_dataset snapshots the arrays on the device): per step only the host tables go up and
+    # come back.  Reported beside `e2e`, which stays the conservative arm (everything re-submitted every step).
+    def e2e_step_resident():
+        ctx.upload_tables()
+        loss = ctx.train_epoch()
+        ctx.sync_to_host()
+        return loss
+    e2e_step_resident()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        flush_l2()
+        e2e_step_resident()
+    barrier()
+    e2e_res_s = reduce(time.perf_counter() - t0)
+
     # ---- evaluation leg ("eval ms" of BASELINE.json's metric): U.I^T on tcgen05 (3xTF32) fused with the masked top-50
     #      and Recall/NDCG/HitRate, on the tables the epochs above trained; every rank evaluates its own user shard.
     ev = None
@@ -492,7 +509,11 @@ def run_gpu_arm(args, rank, world, local_rank):
             "clocks": clk.summary(), "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
-                    "what": "heat_set_dataset + heat_upload_tables + heat_train_epoch + heat_sync_to_host from pinned host buffers"},
+                    "what": "heat_set_dataset + heat_upload_tables + heat_train_epoch + heat_sync_to_host from pinned host buffers",
+                    "dataset_handed_over_once": {"value": n_total * e2e_steps / e2e_res_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_res_s / e2e_steps,
+                                                 "h2d_bytes_per_step": int(uw.nbytes + iw.nbytes + w0.nbytes), "d2h_bytes_per_step": int(d2h),
+                                                 "what": "heat_upload_tables + heat_train_epoch + heat_sync_to_host; the dataset was snapshotted on the device by "
+                                                         "one heat_set_dataset, as the Engine constructor does"}},
             "roofline": roofline, "loss_first_last": [losses[0], losses[-1]], "wall_s_timed_region": wall,
             "update_mode": args.update_mode,
             "engine": {1: "warp-per-sample kernel, fresh-grad update, full grid", 2: "CTA-per-sample kernel", 3: "large-negative kernel"}.get(engine_ran, "?") +
