@@ -653,38 +653,45 @@ eval_kernel(const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ 
 // Recall / NDCG / HitRate at 20 and 50 from the sorted top-k ids (cf/metrics.py:39-48, 87-113,
 // 131-139; natural-log DCG, Recall denominator len(true)+1e-12), one warp per user, summed over
 // users that have test items.  sums[0..5] = R@20, R@50, N@20, N@50, H@20, H@50; sums[6] = users.
+// Lane = rank (two ranks per lane for k = 50): every lane compares its ids with the user's test items (broadcast loads),
+// one ballot per half gives the hit masks; the discounts 1/ln(2+r) and their prefix sums (the ideal DCG) come from a
+// shared-memory table built once per block -- fp64 logarithms per hit made this kernel 0.41 ms of a 4.5 ms evaluation.
 __global__ void metrics_kernel(const int *__restrict__ topk_ids, int k, int U, const long long *__restrict__ test_indptr,
                                const int *__restrict__ test_items, double *sums)
 {
+    __shared__ double disc[64], idcg[65];                 // disc[r] = 1/ln(2+r); idcg[n] = sum_{r<n} disc[r]
+    if (threadIdx.x < 64) disc[threadIdx.x] = 1.0 / log(2.0 + (double)threadIdx.x);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0;
+        idcg[0] = 0.0;
+        for (int r = 0; r < 64; ++r) { a += disc[r]; idcg[r + 1] = a; }
+    }
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    const int kk = k < 50 ? k : 50;
     double acc[7] = {0, 0, 0, 0, 0, 0, 0};
     for (int u = w; u < U; u += nw) {
         const long long tb = test_indptr[u], te = test_indptr[u + 1];
         const long long nt = te - tb;
         if (nt <= 0) continue;
-        int hits20 = 0, hits50 = 0;
-        double dcg20 = 0.0, dcg50 = 0.0;
-        for (int r = 0; r < k && r < 50; ++r) {
-            const int id = topk_ids[(size_t)u * k + r];
-            bool hit = false;
-            for (long long j = tb + lane; j < te; j += 32) hit |= (test_items[j] == id);
-            hit = __any_sync(0xffffffffu, hit) && id >= 0;
-            if (hit) {
-                const double g = 1.0 / log(2.0 + (double)r);
-                hits50 += 1; dcg50 += g;
-                if (r < 20) { hits20 += 1; dcg20 += g; }
-            }
+        const int id0 = lane < kk ? topk_ids[(size_t)u * k + lane] : -1;
+        const int id1 = lane + 32 < kk ? topk_ids[(size_t)u * k + lane + 32] : -1;
+        bool h0 = false, h1 = false;
+        for (long long j = tb; j < te; ++j) {
+            const int t = __ldg(test_items + j);
+            h0 |= t == id0; h1 |= t == id1;
         }
+        const unsigned m0 = __ballot_sync(0xffffffffu, h0 && id0 >= 0), m1 = __ballot_sync(0xffffffffu, h1 && id1 >= 0);
         if (lane == 0) {
-            double idcg20 = 0.0, idcg50 = 0.0;
-            for (int r = 0; r < 50 && r < nt; ++r) {
-                const double g = 1.0 / log(2.0 + (double)r);
-                idcg50 += g;
-                if (r < 20) idcg20 += g;
-            }
+            const int hits20 = __popc(m0 & 0xfffffu), hits50 = __popc(m0) + __popc(m1);
+            double dcg20 = 0.0, dcg50 = 0.0;
+            for (unsigned m = m0; m; m &= m - 1) { const int r = __ffs(m) - 1; dcg50 += disc[r]; if (r < 20) dcg20 += disc[r]; }
+            for (unsigned m = m1; m; m &= m - 1) dcg50 += disc[32 + __ffs(m) - 1];
+            const double i20 = idcg[nt < 20 ? (int)nt : 20], i50 = idcg[nt < 50 ? (int)nt : 50];
             acc[0] += hits20 / ((double)nt + 1e-12); acc[1] += hits50 / ((double)nt + 1e-12);
-            acc[2] += dcg20 / (idcg20 + 1e-12);      acc[3] += dcg50 / (idcg50 + 1e-12);
+            acc[2] += dcg20 / (i20 + 1e-12);         acc[3] += dcg50 / (i50 + 1e-12);
             acc[4] += hits20 > 0 ? 1.0 : 0.0;        acc[5] += hits50 > 0 ? 1.0 : 0.0;
             acc[6] += 1.0;
         }
