@@ -92,23 +92,29 @@ def main():
                 c.close()
         dist.barrier()
 
-    # exchange time at the Amazon-Books table size (91 599 x 64 fp32 + W0), both paths, default rule (mean)
-    big = synth.generate(64, 91599, 4096, seed=3)
-    for mode in (0, 1):
-        t = list(synth.init_tables(big.num_users, big.num_items, 64, seed=7))
-        ctx = make(rank, world, mode, big, t)
-        for _ in range(3):
-            ctx.comm_sync_items()
-        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(20):
-            ctx.comm_sync_items()
-        ctx.sync_to_host()
-        dist.barrier()
-        ms = (time.perf_counter() - t0) / 20 * 1e3
-        if rank == 0:
-            print(f"exchange of 23.4 MB at world {world}: {'fused peer kernel' if mode == 0 else 'NCCL all-reduce path'} {ms:.3f} ms", flush=True)
-        ctx.close()
+    # exchange time by table size (91 599 x 64 fp32 = the Amazon-Books table; 2 M x 64 = BASELINE configs[4]), both paths,
+    # default rule (mean).  Back-to-back exchanges, wall clock over 20 of them; NVLink bytes per rank and exchange =
+    # (world-1)/world of the table read from the peers + the same written to them.
+    for items in (91599, 500000, 2000000):
+        big = synth.generate(64, items, 4096, seed=3, max_degree=64)
+        for mode in (0, 1):
+            t = list(synth.init_tables(big.num_users, big.num_items, 64, seed=7))
+            ctx = make(rank, world, mode, big, t)
+            for _ in range(3):
+                ctx.comm_sync_items()
+            torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(20):
+                ctx.comm_sync_items()
+            ctx.sync_to_host()
+            dist.barrier()
+            ms = (time.perf_counter() - t0) / 20 * 1e3
+            mb = items * 64 * 4 / 1e6
+            if rank == 0:
+                link = 2 * (world - 1) / world * mb / 1e3 / (ms * 1e-3)
+                print(f"exchange of {mb:.1f} MB at world {world}: {'fused peer kernel' if mode == 0 else 'NCCL all-reduce path'} {ms:.3f} ms"
+                      f" = {link:.0f} GB/s of NVLink traffic per rank (read + write)", flush=True)
+            ctx.close()
     if rank == 0:
         print(f"peer exchange check ok at world {world}", flush=True)
     dist.destroy_process_group()
