@@ -49,3 +49,28 @@ def test_host_tile_sampler_twin_matches_oracle():
         clash = tw == clicks[:, 1:2]
         assert np.array_equal(t[~clash], tw[~clash])
     assert abi.tile_draw(11, 3, 99, 5, 500, 0, 1) == abi.philox_draw(11, 3, 99, 5, 500)
+
+
+def test_ctypes_config_layout_matches_the_c_header(tmp_path):
+    """heat_b200/abi.py mirrors `heat_config` by hand: field offsets and the struct size must be the C compiler's."""
+    import ctypes
+    import subprocess
+    fields = [f[0] for f in abi.HeatConfig._fields_]
+    src = '#include <stdio.h>\n#include <stddef.h>\n#include "heat_b200.h"\nint main(void) {\n'
+    for f in fields:
+        src += f'  printf("{f} %zu\\n", offsetof(heat_config, {f}));\n'
+    src += '  printf("sizeof %zu\\n", sizeof(heat_config));\n  return 0;\n}\n'
+    c = tmp_path / "layout.c"
+    c.write_text(src)
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(c), "-o", str(exe)])
+    out = dict(line.split() for line in subprocess.check_output([str(exe)], text=True).splitlines())
+    for f in fields:
+        assert int(out[f]) == getattr(abi.HeatConfig, f).offset, f
+    assert int(out["sizeof"]) == ctypes.sizeof(abi.HeatConfig)
+    # every field of the header is mirrored (a field added to the header only would shift nothing but be unreachable)
+    hdr = open(os.path.join(ROOT, "include", "heat_b200.h")).read()
+    body = hdr[hdr.index("typedef struct heat_config {"):hdr.index("} heat_config;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    declared = re.findall(r"\b(?:uint64_t|uint32_t|float|const uint64_t \*)\s*\**(\w+);", body)
+    assert declared == fields, (declared, fields)
