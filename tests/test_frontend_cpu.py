@@ -25,6 +25,18 @@ def test_cf_c_surface_matches_reference_binding():
     assert isinstance(mf, m.models.Model)
     aw = m.behavior_aggregators.AggregatorWeights(aggregator_weights0=np.zeros((64, 64), np.float32))
     assert aw.emb_dim == 64
+    # additive GPU-path knobs: plain attributes with the library defaults (0), copied by cf_config.CFConfig.init_c_instance
+    for knob in cf_config.GPU_KNOBS:
+        assert hasattr(c, knob), knob
+        if knob != "seed":
+            assert getattr(c, knob) == 0, knob
+    py = cf_config.CFConfig(emb_dim=64, num_negs=16, engine=2, sync_average=2, sync_grads=1, eval_precision=1, w0_tail_mode=1)
+    py.num_users, py.num_items, py.train_size = 10, 20, 5
+    py.init_c_instance()
+    assert (py.c_instance.engine, py.c_instance.sync_average, py.c_instance.sync_grads, py.c_instance.eval_precision,
+            py.c_instance.w0_tail_mode) == (2, 2, 1, 1, 1)
+    with pytest.raises(TypeError):
+        cf_config.CFConfig(emb_dim=64, no_such_knob=1)
     m.test.test_out().test("cf_c surface ok")
     for name in ("train_one_epoch", "evaluate0", "evaluate_topk", "evaluate_metrics", "sync_to_host", "comm_init"):
         assert hasattr(m.train.Engine, name)
