@@ -160,3 +160,27 @@ def test_history_arrays_follow_the_reference_rule():
         assert len(set(his[u].tolist())) == 8 and set(his[u].tolist()) <= set(row.tolist())
     again, _ = datasets._history(indptr, items, 8, seed=3)
     assert np.array_equal(his, again)
+
+
+def test_sub_click_datasets_tile_the_parent(tmp_path):
+    """The multi-rank frontend: user-range shards (main.py:51-66) cover every sample once, keep item ids global, re-base user
+    ids, and carry the global index of their first sample (the Philox counter base)."""
+    from heat_b200.cf import main as cf_main
+    d = synth.generate(211, 300, 6000, max_his=20, seed=9)
+    synth.write_lightgcn_txt(d, str(tmp_path / "train.txt"), str(tmp_path / "test.txt"))
+    cfg = cf_config.CFConfig(emb_dim=32, num_negs=8, max_his=20)
+    parent = datasets.ClickDataset(str(tmp_path / "train.txt"), config=cfg)
+    world, seen, offset = 3, 0, 0
+    for r in range(world):
+        a, b = cf_main.user_range(parent.num_users, r, world)
+        sub = datasets.SubClickDataset(parent, a, b, r)
+        assert sub.num_users == b - a and sub.num_items == parent.num_items
+        assert sub.sample_offset == offset
+        n = sub.click_dataset.shape[0]
+        assert np.array_equal(sub.click_dataset[:, 1], parent.click_dataset[offset:offset + n, 1])
+        assert np.array_equal(sub.click_dataset[:, 0] + np.uint64(a), parent.click_dataset[offset:offset + n, 0])
+        assert np.array_equal(sub.his_items, parent.his_items[a:b]) and np.array_equal(sub.masks, parent.masks[a:b])
+        ip, it = sub.csr()
+        assert ip[-1] == n and np.array_equal(it, parent.items[parent.indptr[a]:parent.indptr[b]])
+        seen += n; offset += n
+    assert seen == parent.click_dataset.shape[0]
