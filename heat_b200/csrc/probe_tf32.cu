@@ -78,6 +78,8 @@ int probe_tf32(int device, int iters, double *tflops)
         if (v == "64t") return probe_tf32_variant<64, true>(device, iters, tflops);
         if (v == "128t") return probe_tf32_variant<128, true>(device, iters, tflops);
         if (v == "256t") return probe_tf32_variant<224, true>(device, iters, tflops);
+        if (v == "96t") return probe_tf32_variant<96, true>(device, iters, tflops);
+        if (v == "192t") return probe_tf32_variant<192, true>(device, iters, tflops);
     }
     return probe_tf32_variant<256, false>(device, iters, tflops);
 }
